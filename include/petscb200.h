@@ -1,0 +1,226 @@
+/* petscb200.h — the C ABI of libpetscb200.so: a B200 (sm_100a) implementation of PETSc's sparse-solve hot path
+ * (AIJ MatMult/MatMultAdd, the MPIAIJ ghost exchange, the Krylov vector kernels, KSPSolve_CG / KSPSolve_GMRES).
+ *
+ * This header is the drop-in boundary.  Everything is `extern "C"`, plain pointers and sizes; `double *` vector
+ * arguments are DEVICE pointers unless the name says `host`.  PetscInt is 32-bit `int`, PetscScalar is `double`
+ * (the reference's default build, include/petscsys.h).  Every function returns a PetscErrorCode-compatible int
+ * (0 = success, otherwise one of the PETSC_ERR_* values of reference include/petscerror.h:41-92, repeated below);
+ * b200_last_error() gives the message.  Reference citations (file:line, relative to the erdc/petsc-dev tree) name
+ * the interface each entry point replaces; INTEGRATION.md shows the Mat/Vec plugin that binds them.
+ *
+ * There is no CPU fallback: a compute entry point called without a usable CUDA device returns B200_ERR_LIB.
+ */
+#ifndef PETSCB200_H
+#define PETSCB200_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- error codes (== reference include/petscerror.h) ------------------------------------------------------- */
+#define B200_ERR_MEM             55
+#define B200_ERR_SUP             56
+#define B200_ERR_ORDER           58
+#define B200_ERR_ARG_SIZ         60
+#define B200_ERR_ARG_IDN         61
+#define B200_ERR_ARG_WRONG       62
+#define B200_ERR_ARG_OUTOFRANGE  63
+#define B200_ERR_FP              72
+#define B200_ERR_ARG_WRONGSTATE  73
+#define B200_ERR_LIB             76
+#define B200_ERR_PLIB            77
+#define B200_ERR_ARG_NULL        85
+
+/* NormType, reference include/petscvec.h:155 */
+#define B200_NORM_1         0
+#define B200_NORM_2         1
+#define B200_NORM_FROBENIUS 2
+#define B200_NORM_INFINITY  3
+#define B200_NORM_1_AND_2   4
+
+/* KSPConvergedReason, reference include/petscksp.h:404-424 */
+#define B200_KSP_CONVERGED_RTOL            2
+#define B200_KSP_CONVERGED_ATOL            3
+#define B200_KSP_CONVERGED_ITERATING       0
+#define B200_KSP_DIVERGED_NULL            -2
+#define B200_KSP_DIVERGED_ITS             -3
+#define B200_KSP_DIVERGED_DTOL            -4
+#define B200_KSP_DIVERGED_BREAKDOWN       -5
+#define B200_KSP_DIVERGED_INDEFINITE_PC   -8
+#define B200_KSP_DIVERGED_NAN             -9
+#define B200_KSP_DIVERGED_INDEFINITE_MAT -10
+
+/* KSPNormType, reference include/petscksp.h (KSP_NORM_NONE..NATURAL) */
+#define B200_KSP_NORM_NONE             0
+#define B200_KSP_NORM_PRECONDITIONED   1
+#define B200_KSP_NORM_UNPRECONDITIONED 2
+#define B200_KSP_NORM_NATURAL          3
+
+typedef struct b200_mat_s     *b200_mat;      /* MATSEQAIJ-on-device, or the MPIAIJ pair (diag, off-diag, ghost plan) */
+typedef struct b200_scatter_s *b200_scatter;  /* device-resident VecScatter (MPI -> Seq ghost gather)               */
+
+/* ---- runtime ------------------------------------------------------------------------------------------------
+ * The reference's GPU types initialise their library in PetscInitialize (src/sys/objects/pinit.c:838-846) and never
+ * pick a device; here the caller does (one process per GPU). */
+int         b200_init(int device);                 /* cudaSetDevice + streams + scratch; idempotent                 */
+int         b200_finalize(void);
+const char *b200_last_error(void);
+int         b200_version(void);
+int         b200_device_count(int *n);
+int         b200_set_stream(void *cuda_stream);    /* run on the caller's stream (NULL = the library's own)         */
+int         b200_get_stream(void **cuda_stream);
+int         b200_synchronize(void);                /* WaitForGPU, src/vec/vec/impls/seq/seqcusp/cuspvecimpl.h:88    */
+int         b200_launch_count(long long *n);       /* number of kernels this library has launched so far           */
+int         b200_timer_start(void);                /* cudaEventRecord on the compute stream                         */
+int         b200_timer_stop(double *milliseconds); /* record + synchronize + elapsed                                */
+int         b200_flush_l2(void);                   /* overwrite a buffer larger than L2 (benchmark hygiene)        */
+
+/* device / pinned memory (VecCUSPAllocateCheck, VecCUSPCopyToGPU, VecCUSPCopyFromGPU:
+ * src/vec/vec/impls/seq/seqcusp/veccusp.cu:68,109,173) */
+int b200_malloc(size_t bytes, void **dptr);
+int b200_free(void *dptr);
+int b200_host_alloc(size_t bytes, void **hptr);    /* pinned */
+int b200_host_free(void *hptr);
+int b200_memcpy_h2d(void *dst, const void *src_host, size_t bytes);   /* stream-ordered, returns when complete    */
+int b200_memcpy_d2h(void *dst_host, const void *src, size_t bytes);
+int b200_memcpy_h2d_async(void *dst, const void *src_host, size_t bytes);
+int b200_memcpy_d2h_async(void *dst_host, const void *src, size_t bytes);
+int b200_memset(void *dst, int byte, size_t bytes);
+
+/* ---- communicator (one rank per GPU) -------------------------------------------------------------------------
+ * Replaces the MPI communicator of VecDot_MPI / VecScatterBegin (src/vec/vec/impls/mpi/pbvec.c:16,
+ * src/vec/vec/utils/vpscat.h:97).  The unique id is produced on rank 0 and handed to the other ranks by the host
+ * program (torch.distributed, MPI_Bcast, a file ...). */
+#define B200_COMM_ID_BYTES 128
+int b200_comm_get_unique_id(void *id128);
+int b200_comm_init(int rank, int size, const void *id128);
+int b200_comm_rank(int *rank, int *size);
+int b200_comm_destroy(void);
+int b200_comm_allreduce_sum(double *dvals, int n);              /* in place, device buffer, stream-ordered        */
+int b200_comm_barrier(void);
+/* peer-memory mode: reductions and the ghost exchange go through NVLink peer stores instead of NCCL */
+int b200_comm_enable_p2p(int enable);
+int b200_comm_p2p_enabled(int *enabled);
+
+/* ---- Vec kernels (device arrays of n doubles) ----------------------------------------------------------------
+ * Each replaces the VECSEQ op named (src/vec/vec/impls/seq/{bvec1,bvec2,dvec2}.c) and the VECSEQCUSP op that
+ * shadows it (src/vec/vec/impls/seq/seqcusp/veccusp.cu); reductions return through HOST pointers and are valid on
+ * return.  Functions without `_local` reduce over the communicator when one is initialised with size > 1
+ * (VecDot_MPI pbvec.c:9, VecNorm_MPI pvec2.c:49, VecMDot_MPI pvec2.c:10). */
+int b200_vec_set(int n, double *x, double alpha);                                   /* VecSet_Seq dvec2.c:722      */
+int b200_vec_copy(int n, const double *x, double *y);                               /* VecCopy_Seq bvec2.c:464     */
+int b200_vec_swap(int n, double *x, double *y);                                     /* VecSwap_Seq bvec2.c:519     */
+int b200_vec_scale(int n, double *x, double alpha);                                 /* VecScale_Seq bvec1.c:183    */
+int b200_vec_axpy(int n, double *y, double alpha, const double *x);                 /* VecAXPY_Seq bvec1.c:244     */
+int b200_vec_aypx(int n, double *y, double alpha, const double *x);                 /* VecAYPX_Seq dvec2.c:971     */
+int b200_vec_axpby(int n, double *y, double alpha, double beta, const double *x);   /* VecAXPBY_Seq bvec1.c:320    */
+int b200_vec_waxpy(int n, double *w, double alpha, const double *x, const double *y); /* VecWAXPY_Seq dvec2.c:1082 */
+int b200_vec_axpbypcz(int n, double *z, double alpha, double beta, double gamma, const double *x, const double *y); /* bvec1.c:418 */
+int b200_vec_pointwise_mult(int n, double *w, const double *x, const double *y);    /* bvec2.c:234                 */
+int b200_vec_pointwise_divide(int n, double *w, const double *x, const double *y);  /* bvec2.c:298                 */
+int b200_vec_reciprocal(int n, double *x);                                          /* VecReciprocal_Default       */
+int b200_vec_maxpy(int n, double *y, int nv, const double *alpha_host, const double *const *x_host_ptrs); /* VecMAXPY_Seq dvec2.c:836 */
+
+int b200_vec_dot(int n, const double *x, const double *y, double *result_host);     /* VecDot_Seq bvec1.c:57 / _MPI */
+int b200_vec_dot_local(int n, const double *x, const double *y, double *result_host);
+int b200_vec_norm(int n, const double *x, int normtype, double *result_host);       /* VecNorm_Seq bvec2.c:605 / _MPI; 2 values for NORM_1_AND_2 */
+int b200_vec_norm_local(int n, const double *x, int normtype, double *result_host);
+int b200_vec_mdot(int n, const double *x, int nv, const double *const *y_host_ptrs, double *result_host); /* VecMDot_Seq dvec2.c:146 / _MPI */
+int b200_vec_mdot_local(int n, const double *x, int nv, const double *const *y_host_ptrs, double *result_host);
+int b200_vec_dotnorm2(int n, const double *s, const double *t, double *dp_host, double *nm_host);  /* VecDotNorm2, veccusp.cu:1816 */
+
+/* ---- Mat (AIJ / CSR) ------------------------------------------------------------------------------------------
+ * b200_mat_create_seqaij uploads an ASSEMBLED host CSR (Mat_SeqAIJ i/j/a, src/mat/impls/aij/seq/aij.h:10-39; column
+ * ids ascending within a row) and bins its rows — what MatAssemblyEnd_SeqAIJCUSP -> MatCUSPCopyToGPU does
+ * (src/mat/impls/aij/seq/seqcusp/aijcusp.cu:126,458).  The host arrays are not retained. */
+int b200_mat_create_seqaij(int m, int n, const int *i_host, const int *j_host, const double *a_host, b200_mat *A);
+int b200_mat_update_values(b200_mat A, const double *a_host);    /* same pattern, new values (value-only re-upload) */
+int b200_mat_destroy(b200_mat A);
+int b200_mat_get_size(b200_mat A, int *m, int *n, long long *nz);
+int b200_mat_mult(b200_mat A, const double *x, double *y);                    /* MatMult_SeqAIJ aij.c:1225 / MatMult_MPIAIJ mpiaij.c:1102       */
+int b200_mat_multadd(b200_mat A, const double *x, const double *y, double *z); /* MatMultAdd_SeqAIJ aij.c:1291 / _MPIAIJ mpiaij.c:1132 ; z may alias y */
+int b200_mat_get_diagonal(b200_mat A, double *d);                             /* MatGetDiagonal_SeqAIJ aij.c:1040 / _MPIAIJ mpiaij.c:1246       */
+int b200_mat_flops(b200_mat A, double *mult_flops);                           /* 2*nz - nonzerorow, aij.c:1281                                 */
+int b200_mat_bytes(b200_mat A, double *mult_bytes);                           /* algorithmic bytes of one MatMult                  */
+int b200_mat_bin_info(b200_mat A, int *ntiles, int *nlong, int *compressed);  /* row-binning summary                                           */
+/* the four fused entry points the CG driver uses (kept public so a KSP plugin can call them) */
+int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double *xdoty_host);   /* y = A x and x.y in one pass (seq, m == n)      */
+
+/* ---- MPIAIJ host-side setup (pure integer work, no GPU needed; bit-exact with the reference) ------------------ */
+/* PetscSplitOwnership / PetscLayoutSetUp: src/sys/utils/psplit.c:88, src/vec/vec/impls/mpi/pmap.c:142-159 */
+int b200_split_ownership(int N, int size, int bs, int *range /* size+1 */);
+/* MatSetValues_MPIAIJ column routing + MatSetUpMultiply_MPIAIJ (src/mat/impls/aij/mpi/mpiaij.c:507-565,
+ * src/mat/impls/aij/mpi/mmaij.c:28-64): split local rows (global column ids, ascending) into the diagonal block
+ * (local ids = col - cstart) and the off-diagonal block (ids into the sorted distinct `garray`).
+ * Call once with NULL outputs to get sizes (nzA, nzB, nghost), then with arrays. */
+int b200_mpiaij_split(int m, int cstart, int cend, const int *i, const int *j, const double *a,
+                      int *Ai, int *Aj, double *Aa, int *Bi, int *Bj, double *Ba, int *garray,
+                      long long *nzA, long long *nzB, int *nghost);
+/* MatCreateColmap_MPIAIJ_Private (mpiaij.c:357-377, dense form): colmap[garray[i]] = i+1, zero elsewhere */
+int b200_mpiaij_colmap(int N, int nghost, const int *garray, int *colmap);
+/* VecScatterCreate_PtoS (src/vec/vec/utils/vpscat.c:1730-1924), receive side and request lists.  inidx[nx] are
+ * (block) indices into the parallel vector (garray for MatMult, mmaij.c:132-143), inidy[nx] the (block) positions in
+ * the sequential vector, bs the block size, range[size+1] the ownership ranges, lengthy the sequential length.
+ * Call with from_procs == NULL to query nfrom / nlocal; arrays must hold size (+1) resp. nx entries.
+ *   from_procs/from_starts/from_indices : the `from` context (vpscat.c:1850-1879)
+ *   req_counts[size] (own rank zeroed), req_values : wanted global ids grouped by owner, ascending (vpscat.c:1798-1806)
+ *   to_local/from_local[nlocal] : the self part (vpscat.c:1890-1903)                                              */
+int b200_scatter_plan_from(int nx, const int *inidx, const int *inidy, int bs, int size, const int *range, int rank,
+                           int lengthy, int *nfrom, int *from_procs, int *from_starts, int *from_indices,
+                           int *req_counts, int *req_values, int *nlocal, int *to_local, int *from_local);
+/* send side (vpscat.c:1827-1848): nto requesting ranks in ascending order (PetscSortMPIIntWithArray, :1780) with
+ * lengths[nto] and their concatenated requested GLOBAL ids; outputs to_starts[nto+1], to_indices = id - rstart. */
+int b200_scatter_plan_to(int nto, const int *lengths, const int *requested_global, int rstart, int rend,
+                         int *to_starts, int *to_indices);
+/* mmaij.c:106-128: may the ghost list be described by a block index set of size bs? */
+int b200_mpiaij_use_block_is(int nghost, const int *garray, int bs, int *use);
+/* assemble the device-resident MPIAIJ operator from the pieces above.  The ghost exchange goes rank-to-rank over
+ * NCCL (or peer stores when p2p is enabled) on a side stream, overlapped with the diagonal-block product
+ * (MatMult_MPIAIJ mpiaij.c:1102-1116; MatMult_MPIAIJCUSP mpiaijcusp.cu:85-112). */
+int b200_mat_create_mpiaij(int m, int n_local, int N,
+                           const int *Ai, const int *Aj, const double *Aa,
+                           int nghost, const int *Bi, const int *Bj, const double *Ba, const int *garray,
+                           int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                           int nfrom, const int *from_procs, const int *from_starts,
+                           b200_mat *A);
+int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost);         /* Mat_MPIAIJ::lvec, mpiaij.h:60   */
+int b200_mat_mpiaij_scatter(b200_mat A, const double *x);                     /* VecScatterBegin+End only        */
+
+/* ---- KSP drivers ----------------------------------------------------------------------------------------------
+ * Restatements of KSPSolve_CG (src/ksp/ksp/impls/cg/cg.c:92-286) and KSPSolve_GMRES / KSPGMRESCycle
+ * (src/ksp/ksp/impls/gmres/gmres.c:118-238, borthog2.c:35-118) with PCJACOBI / PCNONE
+ * (src/ksp/pc/impls/jacobi/jacobi.c:125-206,266-278) and KSPDefaultConverged (src/ksp/ksp/interface/iterativ.c:702).
+ * The scalar recurrences stay on the host exactly as in the reference; the vector work is the kernels above plus
+ * fused forms of them. */
+typedef struct {
+  int    ksp_type;           /* 0 = cg, 1 = gmres                                                                */
+  int    pc_type;            /* 0 = none, 1 = jacobi                                                             */
+  double rtol, abstol, dtol; /* KSPSetTolerances; defaults 1e-5, 1e-50, 1e5                                      */
+  int    max_it;             /* default 10000                                                                    */
+  int    norm_type;          /* B200_KSP_NORM_*; CG default PRECONDITIONED (cg.c:439), GMRES PRECONDITIONED      */
+  int    guess_nonzero;      /* KSPSetInitialGuessNonzero                                                        */
+  int    gmres_restart;      /* default 30 (gmres.c:947)                                                         */
+  int    gmres_cgs_refine;   /* 0 never (default), 1 ifneeded, 2 always (borthog2.c:43,85-108)                   */
+  double gmres_haptol;       /* default 1e-30                                                                    */
+  int    fused;              /* 0 = op-by-op exactly like the reference's call sequence; 1 = fused kernels       */
+  int    check_every;        /* fused CG only: host looks at the device-side convergence flag every k iterations */
+} b200_ksp_options;
+int b200_ksp_default_options(b200_ksp_options *o);
+typedef struct {
+  int    its;                /* KSPGetIterationNumber                                                            */
+  int    reason;             /* KSPGetConvergedReason                                                            */
+  int    nhist;              /* entries written to the residual history                                          */
+  double rnorm;              /* last residual norm                                                               */
+  double solve_ms;           /* device time of the solve (CUDA events), setup excluded                           */
+} b200_ksp_result;
+/* x, b device vectors of the matrix's local row count; hist_host may be NULL.  PCSetUp (diagonal extraction) is
+ * done before the timed region like KSPSetUp (itfunc.c:376). */
+int b200_ksp_solve(b200_mat A, const b200_ksp_options *o, const double *b, double *x,
+                   double *hist_host, int histmax, b200_ksp_result *result);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PETSCB200_H */

@@ -1,0 +1,110 @@
+/* b200_internal.h — shared state of libpetscb200 (one process = one rank = one B200). */
+#ifndef B200_INTERNAL_H
+#define B200_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdarg.h>
+#include <string.h>
+#include <stdlib.h>
+#include "petscb200.h"
+
+#define B200_MAX_RANKS   16
+#define B200_NSM         148           /* B200: 148 SMs; grids are sized in multiples of it                        */
+#define B200_RED_MAXV    32            /* values one reduction launch can produce (VecMDot chunk)                  */
+#define B200_RED_MAXBLK  (B200_NSM * 8)
+#define B200_RES_SLOTS   256           /* doubles in the pinned/mapped result buffer                              */
+
+struct B200P2P;                         /* peer-memory state, b200_comm.cu */
+
+struct B200Ctx {
+  bool         inited;
+  int          device;
+  int          nsm;
+  cudaStream_t own_stream, stream, comm_stream;
+  cudaEvent_t  ev_t0, ev_t1, ev_fork, ev_join;
+  double      *h_res;        /* pinned + mapped host memory: reductions land here                                  */
+  double      *d_res;        /* device alias of h_res                                                              */
+  double      *d_partials;   /* [B200_RED_MAXBLK * B200_RED_MAXV]                                                  */
+  unsigned    *d_ticket;     /* last-block tickets (one per concurrent reduction slot)                             */
+  double      *d_scal;       /* device scalars (allreduce staging, fused-CG state)                                 */
+  void        *d_ptrtab;     /* device copy of pointer tables for MDot/MAXPY                                        */
+  void        *h_ptrtab;     /* pinned staging for the same                                                        */
+  void        *l2flush;
+  size_t       l2bytes;
+  long long    launches;
+  /* communicator */
+  int          rank, size;
+  void        *nccl;         /* ncclComm_t                                                                         */
+  bool         p2p;
+  B200P2P     *peer;
+};
+
+extern B200Ctx g_b200;
+
+int  b200_seterr(int code, const char *fmt, ...);
+int  b200_cuda_err(cudaError_t e, const char *what, const char *file, int line);
+bool b200_ready(void);
+
+#define B200_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return b200_cuda_err(e__, #call, __FILE__, __LINE__); } while (0)
+#define B200_CHK(call)  do { int r__ = (call); if (r__) return r__; } while (0)
+#define B200_NEED_INIT() do { if (!g_b200.inited) { int r__ = b200_init(-1); if (r__) return r__; } } while (0)
+#define B200_LAUNCHED(k) do { g_b200.launches += (k); cudaError_t e__ = cudaGetLastError(); if (e__ != cudaSuccess) return b200_cuda_err(e__, "kernel launch", __FILE__, __LINE__); } while (0)
+
+/* ---- matrices ------------------------------------------------------------------------------------------------ */
+struct B200Seq {              /* one CSR block on the device + its row binning                                        */
+  int        m, n;
+  long long  nz;
+  int        nonzerorow;      /* rows with at least one entry (flop count 2 nz - nonzerorow, aij.c:1281)            */
+  int       *d_i;             /* [m+1] row offsets                                                                   */
+  int       *d_j;             /* [nz + pad] column ids                                                               */
+  double    *d_a;             /* [nz + pad] values                                                                   */
+  bool       compressed;      /* rows are visited through the non-empty-row list (compressedrow, aij.h:99-115)       */
+  int        ncrows;          /* rows in the visiting order (m, or the number of non-empty rows)                     */
+  int       *d_ci;            /* [ncrows+1] offsets in visiting order (== d_i when not compressed)                   */
+  int       *d_rindex;        /* [ncrows] visiting order -> row id (NULL when not compressed)                        */
+  int        ntiles;          /* stream tiles: contiguous runs of short rows, <= TILE_NNZ entries each               */
+  int4      *d_tiles;         /* {row_begin, row_end, k_begin, k_end} in visiting order                              */
+  int        nlong;           /* rows longer than LONG_THRESH, one CTA each                                          */
+  int       *d_long;          /* their positions in visiting order                                                   */
+  double    *d_dotpart;       /* [ntiles + nlong] per-CTA partials of the fused x.y                                  */
+};
+
+struct b200_mat_s {
+  int      kind;              /* 0 = SeqAIJ, 1 = MPIAIJ                                                               */
+  B200Seq  A;                 /* the matrix (seq) or the diagonal block (mpi)                                         */
+  /* MPIAIJ part (Mat_MPIAIJ, src/mat/impls/aij/mpi/mpiaij.h:34-77) */
+  B200Seq  B;                 /* off-diagonal block, columns index garray / lvec                                      */
+  int      N;                 /* global columns                                                                       */
+  int      nghost;
+  int     *d_garray;          /* [nghost] sorted global ids of the ghost columns                                      */
+  double  *d_lvec[2];         /* ghost values (double-buffered for the peer-store exchange)                           */
+  int      nto, nfrom;
+  int     *to_procs, *to_starts, *from_procs, *from_starts;   /* host copies of the VecScatter lists                 */
+  int     *d_to_indices;      /* [to_starts[nto]] local offsets to pack                                               */
+  double  *d_sendbuf;         /* packed send values                                                                   */
+  long long epoch;            /* exchange counter                                                                     */
+  void    *peerplan;          /* per-matrix peer-store plan (b200_comm.cu)                                            */
+};
+
+int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
+void b200_seq_free(B200Seq *S);
+int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
+
+/* internal cross-file entry points */
+int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_max /*0 sum, 1 max*/);
+int b200_comm_allreduce_dev(double *dvals, int n, int op_max);
+int b200_mpiaij_exchange_begin(b200_mat A, const double *x);
+int b200_mpiaij_exchange_end(b200_mat A);
+
+/* reduction grid helper */
+static inline int b200_red_grid(long long n, int threads, int per_thread)
+{
+  long long g = (n + (long long)threads * per_thread - 1) / ((long long)threads * per_thread);
+  if (g < 1) g = 1;
+  if (g > B200_RED_MAXBLK) g = B200_RED_MAXBLK;
+  return (int)g;
+}
+
+#endif
