@@ -187,6 +187,7 @@ int b200_mat_create_mpiaij(int m, int n_local, int N,
                            b200_mat *A);
 int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost);         /* Mat_MPIAIJ::lvec, mpiaij.h:60   */
 int b200_mat_mpiaij_scatter(b200_mat A, const double *x);                     /* VecScatterBegin+End only        */
+int b200_mat_mpiaij_set_lvec(b200_mat A, const double *ghost_values_dev);     /* caller-performed scatter (P virtual ranks in one process) */
 
 /* ---- KSP drivers ----------------------------------------------------------------------------------------------
  * Restatements of KSPSolve_CG (src/ksp/ksp/impls/cg/cg.c:92-286) and KSPSolve_GMRES / KSPGMRESCycle

@@ -1,0 +1,316 @@
+"""petsc-dev_b200 — host-side mirror of the reference's Mat / Vec / KSP interface for the sparse-solve hot path,
+bound to libpetscb200.so (include/petscb200.h) through ctypes.
+
+The directory name is not a Python identifier; import it with
+    import importlib; pb = importlib.import_module("petsc-dev_b200")
+
+There is NO CPU fallback: if the CUDA library is missing this module raises at import, and every compute call
+raises PetscB200Error when no B200 is present.  Nothing here imports oracle/.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libpetscb200.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "petscb200.h")
+
+if not os.path.exists(LIB_PATH):
+    raise ImportError("%s is not built: run `python -c 'import __graft_entry__ as g; g.build()'` or "
+                      "`make -C petsc-dev_b200/csrc` (there is no CPU fallback)" % LIB_PATH)
+lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+lib.b200_last_error.restype = C.c_char_p
+
+NORM_1, NORM_2, NORM_FROBENIUS, NORM_INFINITY, NORM_1_AND_2 = 0, 1, 2, 3, 4
+KSP_NORM_NONE, KSP_NORM_PRECONDITIONED, KSP_NORM_UNPRECONDITIONED, KSP_NORM_NATURAL = 0, 1, 2, 3
+KSPCG, KSPGMRES = 0, 1
+PCNONE, PCJACOBI = 0, 1
+
+c_dp = C.POINTER(C.c_double)
+c_ip = C.POINTER(C.c_int)
+
+
+class PetscB200Error(RuntimeError):
+    def __init__(self, code, what):
+        self.code = code
+        RuntimeError.__init__(self, "%s: PetscErrorCode %d: %s" % (what, code, lib.b200_last_error().decode()))
+
+
+def _chk(rc, what):
+    if rc:
+        raise PetscB200Error(rc, what)
+
+
+def _ip(a):
+    return a.ctypes.data_as(c_ip) if a is not None else None
+
+
+def _dp(a):
+    return a.ctypes.data_as(c_dp) if a is not None else None
+
+
+def _i32(a):
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _f64(a):
+    return np.ascontiguousarray(a, dtype=np.float64)
+
+
+def init(device=-1):
+    _chk(lib.b200_init(int(device)), "b200_init")
+
+
+def finalize():
+    _chk(lib.b200_finalize(), "b200_finalize")
+
+
+def synchronize():
+    _chk(lib.b200_synchronize(), "b200_synchronize")
+
+
+def launch_count():
+    n = C.c_longlong()
+    lib.b200_launch_count(C.byref(n))
+    return n.value
+
+
+def timer_start():
+    _chk(lib.b200_timer_start(), "timer_start")
+
+
+def timer_stop():
+    ms = C.c_double()
+    _chk(lib.b200_timer_stop(C.byref(ms)), "timer_stop")
+    return ms.value
+
+
+def flush_l2():
+    _chk(lib.b200_flush_l2(), "flush_l2")
+
+
+class Vec:
+    """A device-resident vector of n doubles (VECSEQB200 / the local part of VECMPIB200)."""
+
+    def __init__(self, n, host=None, ptr=None):
+        self.n = int(n)
+        self._own = ptr is None
+        if ptr is None:
+            p = C.c_void_p()
+            _chk(lib.b200_malloc(C.c_size_t(8 * max(self.n, 2)), C.byref(p)), "VecCreate")
+            self.ptr = p.value
+            if host is not None:
+                self.set_array(host)
+            else:
+                self.set(0.0)
+        else:
+            self.ptr = ptr
+
+    # --- host <-> device (VecCUSPCopyToGPU / FromGPU) ---
+    def set_array(self, host):
+        h = _f64(host)
+        if h.size != self.n:
+            raise PetscB200Error(60, "VecSetValues size")
+        _chk(lib.b200_memcpy_h2d(C.c_void_p(self.ptr), h.ctypes.data_as(C.c_void_p), C.c_size_t(8 * self.n)), "H2D")
+        return self
+
+    def get_array(self, out=None):
+        out = np.empty(self.n, np.float64) if out is None else out
+        _chk(lib.b200_memcpy_d2h(out.ctypes.data_as(C.c_void_p), C.c_void_p(self.ptr), C.c_size_t(8 * self.n)), "D2H")
+        return out
+
+    @property
+    def p(self):
+        return C.cast(C.c_void_p(self.ptr), c_dp)
+
+    def offset(self, k):
+        """A non-owning view starting at element k (tests use it for unaligned pointers)."""
+        return Vec(self.n - k, ptr=self.ptr + 8 * k)
+
+    def duplicate(self):
+        return Vec(self.n)
+
+    def destroy(self):
+        if self._own and self.ptr:
+            lib.b200_free(C.c_void_p(self.ptr))
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    # --- the reference's Vec API names ---
+    def set(self, alpha):
+        _chk(lib.b200_vec_set(self.n, self.p, C.c_double(alpha)), "VecSet")
+
+    def copy(self, y):                      # VecCopy(x, y)
+        _chk(lib.b200_vec_copy(self.n, self.p, y.p), "VecCopy")
+
+    def swap(self, y):
+        _chk(lib.b200_vec_swap(self.n, self.p, y.p), "VecSwap")
+
+    def scale(self, alpha):
+        _chk(lib.b200_vec_scale(self.n, self.p, C.c_double(alpha)), "VecScale")
+
+    def axpy(self, alpha, x):               # VecAXPY(y, alpha, x)
+        _chk(lib.b200_vec_axpy(self.n, self.p, C.c_double(alpha), x.p), "VecAXPY")
+
+    def aypx(self, alpha, x):               # VecAYPX(y, alpha, x)
+        _chk(lib.b200_vec_aypx(self.n, self.p, C.c_double(alpha), x.p), "VecAYPX")
+
+    def axpby(self, alpha, beta, x):        # VecAXPBY(y, alpha, beta, x)
+        _chk(lib.b200_vec_axpby(self.n, self.p, C.c_double(alpha), C.c_double(beta), x.p), "VecAXPBY")
+
+    def waxpy(self, alpha, x, y):           # VecWAXPY(w, alpha, x, y)
+        _chk(lib.b200_vec_waxpy(self.n, self.p, C.c_double(alpha), x.p, y.p), "VecWAXPY")
+
+    def axpbypcz(self, alpha, beta, gamma, x, y):   # VecAXPBYPCZ(z, alpha, beta, gamma, x, y)
+        _chk(lib.b200_vec_axpbypcz(self.n, self.p, C.c_double(alpha), C.c_double(beta), C.c_double(gamma), x.p, y.p),
+             "VecAXPBYPCZ")
+
+    def pointwise_mult(self, x, y):         # VecPointwiseMult(w, x, y)
+        _chk(lib.b200_vec_pointwise_mult(self.n, self.p, x.p, y.p), "VecPointwiseMult")
+
+    def pointwise_divide(self, x, y):
+        _chk(lib.b200_vec_pointwise_divide(self.n, self.p, x.p, y.p), "VecPointwiseDivide")
+
+    def reciprocal(self):
+        _chk(lib.b200_vec_reciprocal(self.n, self.p), "VecReciprocal")
+
+    def maxpy(self, alphas, xs):            # VecMAXPY(y, nv, alpha, x[])
+        nv = len(xs)
+        al = _f64(alphas) if nv else np.zeros(1)
+        tab = (c_dp * max(nv, 1))(*[x.p for x in xs])
+        _chk(lib.b200_vec_maxpy(self.n, self.p, nv, _dp(al), tab), "VecMAXPY")
+
+    def dot(self, y, local=False):          # VecDot(x, y)
+        r = C.c_double()
+        f = lib.b200_vec_dot_local if local else lib.b200_vec_dot
+        _chk(f(self.n, self.p, y.p, C.byref(r)), "VecDot")
+        return r.value
+
+    tdot = dot
+
+    def norm(self, ntype=NORM_2, local=False):
+        r = (C.c_double * 2)()
+        f = lib.b200_vec_norm_local if local else lib.b200_vec_norm
+        _chk(f(self.n, self.p, int(ntype), r), "VecNorm")
+        return (r[0], r[1]) if ntype == NORM_1_AND_2 else r[0]
+
+    def mdot(self, ys, local=False):        # VecMDot(x, nv, y[])
+        nv = len(ys)
+        z = np.zeros(max(nv, 1))
+        tab = (c_dp * max(nv, 1))(*[y.p for y in ys])
+        f = lib.b200_vec_mdot_local if local else lib.b200_vec_mdot
+        _chk(f(self.n, self.p, nv, tab, _dp(z)), "VecMDot")
+        return z[:nv]
+
+    def dotnorm2(self, t):                  # VecDotNorm2(s, t) -> (s.t, t.t)
+        a, b = C.c_double(), C.c_double()
+        _chk(lib.b200_vec_dotnorm2(self.n, self.p, t.p, C.byref(a), C.byref(b)), "VecDotNorm2")
+        return a.value, b.value
+
+
+class KSPResult(C.Structure):
+    _fields_ = [("its", C.c_int), ("reason", C.c_int), ("nhist", C.c_int), ("rnorm", C.c_double),
+                ("solve_ms", C.c_double)]
+
+
+class KSPOptions(C.Structure):
+    _fields_ = [("ksp_type", C.c_int), ("pc_type", C.c_int), ("rtol", C.c_double), ("abstol", C.c_double),
+                ("dtol", C.c_double), ("max_it", C.c_int), ("norm_type", C.c_int), ("guess_nonzero", C.c_int),
+                ("gmres_restart", C.c_int), ("gmres_cgs_refine", C.c_int), ("gmres_haptol", C.c_double),
+                ("fused", C.c_int), ("check_every", C.c_int)]
+
+
+class Mat:
+    """An assembled AIJ matrix on the device: MATSEQAIJB200 (from_csr) or MATMPIAIJB200 (parallel.create_mpiaij)."""
+
+    def __init__(self, handle, m, n):
+        self.h = handle
+        self.m, self.n = int(m), int(n)
+
+    @classmethod
+    def from_csr(cls, m, n, ai, aj, aa):
+        ai, aj, aa = _i32(ai), _i32(aj), _f64(aa)
+        h = C.c_void_p()
+        _chk(lib.b200_mat_create_seqaij(int(m), int(n), _ip(ai), _ip(aj), _dp(aa), C.byref(h)), "MatAssemblyEnd (upload)")
+        return cls(h, m, n)
+
+    def update_values(self, aa):
+        aa = _f64(aa)
+        _chk(lib.b200_mat_update_values(self.h, _dp(aa)), "MatAssemblyEnd (values)")
+
+    def destroy(self):
+        if self.h:
+            lib.b200_mat_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+    def get_vecs(self):                     # MatGetVecs -> (right, left)
+        return Vec(self.n), Vec(self.m)
+
+    def mult(self, x, y):                   # MatMult(A, x, y)
+        _chk(lib.b200_mat_mult(self.h, x.p, y.p), "MatMult")
+
+    def mult_add(self, x, y, z):            # MatMultAdd(A, x, y, z)
+        _chk(lib.b200_mat_multadd(self.h, x.p, y.p, z.p), "MatMultAdd")
+
+    def mult_dot(self, x, y):
+        r = C.c_double()
+        _chk(lib.b200_mat_mult_dot(self.h, x.p, y.p, C.byref(r)), "MatMult+VecDot")
+        return r.value
+
+    def get_diagonal(self, d):
+        _chk(lib.b200_mat_get_diagonal(self.h, d.p), "MatGetDiagonal")
+
+    def flops(self):
+        f = C.c_double()
+        _chk(lib.b200_mat_flops(self.h, C.byref(f)), "flops")
+        return f.value
+
+    def bytes(self):
+        f = C.c_double()
+        _chk(lib.b200_mat_bytes(self.h, C.byref(f)), "bytes")
+        return f.value
+
+    def nnz(self):
+        nz = C.c_longlong()
+        _chk(lib.b200_mat_get_size(self.h, None, None, C.byref(nz)), "MatGetInfo")
+        return nz.value
+
+    def bin_info(self):
+        a, b, c = C.c_int(), C.c_int(), C.c_int()
+        _chk(lib.b200_mat_bin_info(self.h, C.byref(a), C.byref(b), C.byref(c)), "bin_info")
+        return dict(ntiles=a.value, nlong=b.value, compressed=bool(c.value))
+
+
+def ksp_options(**kw):
+    o = KSPOptions()
+    _chk(lib.b200_ksp_default_options(C.byref(o)), "KSPCreate")
+    names = {"cg": KSPCG, "gmres": KSPGMRES, "none": PCNONE, "jacobi": PCJACOBI}
+    for k, v in kw.items():
+        if isinstance(v, str):
+            v = names[v]
+        setattr(o, k, v)
+    return o
+
+
+def ksp_solve(A, b, x, histmax=None, **kw):
+    """KSPSolve(ksp, b, x): returns dict(its, reason, history, rnorm, solve_ms).  Keyword options are the fields of
+    b200_ksp_options (ksp_type='cg'|'gmres', pc_type='jacobi'|'none', rtol, abstol, dtol, max_it, norm_type,
+    guess_nonzero, gmres_restart, gmres_cgs_refine, fused, check_every)."""
+    o = ksp_options(**kw)
+    histmax = (o.max_it + 2) if histmax is None else int(histmax)
+    hist = np.zeros(max(histmax, 1))
+    res = KSPResult()
+    _chk(lib.b200_ksp_solve(A.h, C.byref(o), b.p, x.p, _dp(hist), histmax, C.byref(res)), "KSPSolve")
+    return dict(its=res.its, reason=res.reason, history=hist[:res.nhist].copy(), rnorm=res.rnorm, solve_ms=res.solve_ms)

@@ -175,6 +175,16 @@ extern "C" int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost)
   return 0;
 }
 
+/* fill the ghost vector directly (single-process emulation of P ranks: the caller plays the scatter) */
+extern "C" int b200_mat_mpiaij_set_lvec(b200_mat A, const double *ghost_values_dev)
+{
+  B200_NEED_INIT();
+  if (!A || A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
+  for (int k = 0; k < 2; k++)
+    if (A->nghost) B200_CUDA(cudaMemcpyAsync(A->d_lvec[k], ghost_values_dev, sizeof(double) * (size_t)A->nghost, cudaMemcpyDeviceToDevice, g_b200.stream));
+  return 0;
+}
+
 /* VecScatterBegin: pack on the compute stream (x was produced there), then the sends/receives on the side stream so
  * the diagonal-block product that follows on the compute stream overlaps them. */
 int b200_mpiaij_exchange_begin(b200_mat A, const double *x)

@@ -1,0 +1,169 @@
+"""Row-partitioned (MPIAIJ) assembly over one-process-per-GPU ranks.
+
+Host-side plumbing only: the integer structures come from the C ABI (b200_mpiaij_split, b200_scatter_plan_from/_to —
+restatements of MatSetUpMultiply_MPIAIJ, src/mat/impls/aij/mpi/mmaij.c:9-161, and VecScatterCreate_PtoS,
+src/vec/vec/utils/vpscat.c:1730-1924); the request lists travel between ranks with torch.distributed (gloo on CPU,
+nccl on GPUs), which stands in for the Isend/Irecv of vpscat.c:1778-1822.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import Mat, PetscB200Error, _chk, _dp, _f64, _i32, _ip, lib
+
+
+def split_ownership(N, size, bs=1):
+    """PetscSplitOwnership / PetscLayoutSetUp -> range[size+1]."""
+    r = np.zeros(size + 1, np.int32)
+    _chk(lib.b200_split_ownership(int(N), int(size), int(bs), _ip(r)), "PetscLayoutSetUp")
+    return r
+
+
+def mpiaij_split(m, cstart, cend, ai, aj, aa):
+    """Local rows (global column ids) -> dict(Ai, Aj, Aa, Bi, Bj, Ba, garray)."""
+    ai, aj, aa = _i32(ai), _i32(aj), _f64(aa)
+    nzA, nzB, ng = C.c_longlong(), C.c_longlong(), C.c_int()
+    _chk(lib.b200_mpiaij_split(int(m), int(cstart), int(cend), _ip(ai), _ip(aj), _dp(aa), None, None, None, None, None,
+                               None, None, C.byref(nzA), C.byref(nzB), C.byref(ng)), "MatSetUpMultiply (sizes)")
+    out = dict(Ai=np.zeros(m + 1, np.int32), Aj=np.zeros(max(nzA.value, 1), np.int32), Aa=np.zeros(max(nzA.value, 1)),
+               Bi=np.zeros(m + 1, np.int32), Bj=np.zeros(max(nzB.value, 1), np.int32), Ba=np.zeros(max(nzB.value, 1)),
+               garray=np.zeros(max(ng.value, 1), np.int32))
+    _chk(lib.b200_mpiaij_split(int(m), int(cstart), int(cend), _ip(ai), _ip(aj), _dp(aa), _ip(out["Ai"]), _ip(out["Aj"]),
+                               _dp(out["Aa"]), _ip(out["Bi"]), _ip(out["Bj"]), _dp(out["Ba"]), _ip(out["garray"]),
+                               C.byref(nzA), C.byref(nzB), C.byref(ng)), "MatSetUpMultiply")
+    out["Aj"], out["Aa"] = out["Aj"][:nzA.value], out["Aa"][:nzA.value]
+    out["Bj"], out["Ba"] = out["Bj"][:nzB.value], out["Ba"][:nzB.value]
+    out["garray"] = out["garray"][:ng.value]
+    return out
+
+
+def colmap(N, garray):
+    cm = np.zeros(N, np.int32)
+    g = _i32(garray)
+    _chk(lib.b200_mpiaij_colmap(int(N), int(g.size), _ip(g), _ip(cm)), "MatCreateColmap")
+    return cm
+
+
+def use_block_is(garray, bs):
+    g = _i32(garray)
+    u = C.c_int()
+    _chk(lib.b200_mpiaij_use_block_is(int(g.size), _ip(g), int(bs), C.byref(u)), "useblockis")
+    return bool(u.value)
+
+
+def scatter_plan_from(inidx, inidy, bs, ranges, rank, lengthy):
+    """Receive side + request lists of VecScatterCreate_PtoS for this rank."""
+    inidx, inidy, ranges = _i32(inidx), _i32(inidy), _i32(ranges)
+    nx, size = inidx.size, ranges.size - 1
+    nfrom, nlocal = C.c_int(), C.c_int()
+    fp, fs, fi = np.zeros(size, np.int32), np.zeros(size + 1, np.int32), np.zeros(max(nx, 1), np.int32)
+    rc, rv = np.zeros(size, np.int32), np.zeros(max(nx, 1), np.int32)
+    tl, fl = np.zeros(max(nx, 1), np.int32), np.zeros(max(nx, 1), np.int32)
+    _chk(lib.b200_scatter_plan_from(nx, _ip(inidx), _ip(inidy), int(bs), size, _ip(ranges), int(rank), int(lengthy),
+                                    C.byref(nfrom), _ip(fp), _ip(fs), _ip(fi), _ip(rc), _ip(rv), C.byref(nlocal),
+                                    _ip(tl), _ip(fl)), "VecScatterCreate_PtoS (from)")
+    nf, nl = nfrom.value, nlocal.value
+    nreq = int(rc.sum())
+    return dict(nfrom=nf, from_procs=fp[:nf].copy(), from_starts=fs[:nf + 1].copy(), from_indices=fi[:nreq].copy(),
+                req_counts=rc, req_values=rv[:nreq].copy(), nlocal=nl, to_local=tl[:nl].copy(), from_local=fl[:nl].copy())
+
+
+def scatter_plan_to(procs, lengths, requested, rstart, rend):
+    lengths, requested = _i32(lengths), _i32(requested)
+    nto = lengths.size
+    ts, ti = np.zeros(nto + 1, np.int32), np.zeros(max(requested.size, 1), np.int32)
+    _chk(lib.b200_scatter_plan_to(nto, _ip(lengths), _ip(requested), int(rstart), int(rend), _ip(ts), _ip(ti)),
+         "VecScatterCreate_PtoS (to)")
+    return dict(nto=nto, to_procs=_i32(procs), to_starts=ts, to_indices=ti[:requested.size].copy())
+
+
+def exchange_requests(plan, rank, size, dist=None, device="cpu"):
+    """PetscGatherMessageLengths + the Isend/Irecv of the wanted-index lists (vpscat.c:1778-1822) over
+    torch.distributed: returns (procs ascending, lengths, concatenated requested ids) as seen by the OWNER."""
+    import torch
+    import torch.distributed as td
+    dist = dist or td
+    counts = torch.tensor(plan["req_counts"], dtype=torch.int32, device=device)
+    allc = [torch.zeros(size, dtype=torch.int32, device=device) for _ in range(size)]
+    dist.all_gather(allc, counts)
+    allc = torch.stack(allc).cpu().numpy()                 # allc[r][p] = what rank r wants from p
+    # index lists: all_gather of the padded request arrays (setup-time, tiny next to the matrix)
+    maxlen = int(allc.sum(axis=1).max()) if size else 0
+    mine = torch.zeros(max(maxlen, 1), dtype=torch.int32, device=device)
+    rv = plan["req_values"]
+    if rv.size:
+        mine[:rv.size] = torch.tensor(rv, dtype=torch.int32, device=device)
+    allv = [torch.zeros_like(mine) for _ in range(size)]
+    dist.all_gather(allv, mine)
+    procs, lengths, req = [], [], []
+    for r in range(size):                                  # ascending requester rank = PetscSortMPIIntWithArray order
+        c = int(allc[r][rank])
+        if r == rank or c == 0:
+            continue
+        off = int(allc[r][:rank].sum())
+        procs.append(r); lengths.append(c)
+        req.append(allv[r][off:off + c].cpu().numpy())
+    req = np.concatenate(req).astype(np.int32) if req else np.zeros(0, np.int32)
+    return np.array(procs, np.int32), np.array(lengths, np.int32), req
+
+
+def setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=1, dist=None, device="cpu"):
+    """Everything MatAssemblyEnd_MPIAIJ + MatSetUpMultiply_MPIAIJ decide on the host for this rank."""
+    rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
+    m = rend - rstart
+    sp = mpiaij_split(m, rstart, rend, ai, aj, aa)
+    g = sp["garray"]
+    blk = use_block_is(g, bs)
+    if blk:                                                # ISCreateBlock(bs, ec/bs, garray[i*bs]/bs), mmaij.c:130-136
+        inidx = (g[::bs] // bs).astype(np.int32)
+        inidy = np.arange(g.size // bs, dtype=np.int32)
+        pbs = bs
+    else:
+        inidx, inidy, pbs = g, np.arange(g.size, dtype=np.int32), 1
+    frm = scatter_plan_from(inidx, inidy, pbs, ranges, rank, g.size)
+    if size > 1:
+        procs, lengths, req = exchange_requests(frm, rank, size, dist, device)
+    else:
+        procs, lengths, req = np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32)
+    to = scatter_plan_to(procs, lengths, req, rstart, rend)
+    return dict(split=sp, from_=frm, to=to, bs=pbs, m=m, rstart=rstart, rend=rend, N=int(N), block_is=blk)
+
+
+def expand_bs(starts, indices, bs):
+    """Block lists -> scalar lists (what VecScatterInitializeForGPU does, vscatcusp.c:60-100)."""
+    if bs == 1:
+        return _i32(starts), _i32(indices)
+    idx = (np.asarray(indices, np.int64)[:, None] + np.arange(bs)[None, :]).reshape(-1)
+    return _i32(np.asarray(starts, np.int64) * bs), _i32(idx)
+
+
+def create_mpiaij(host):
+    """Upload: the device-resident MATMPIAIJB200 of this rank."""
+    sp, frm, to, bs = host["split"], host["from_"], host["to"], host["bs"]
+    ts, ti = expand_bs(to["to_starts"], to["to_indices"], bs)
+    fs, _ = expand_bs(frm["from_starts"], frm["from_indices"], bs)
+    h = C.c_void_p()
+    m = host["m"]
+    g = _i32(sp["garray"])
+    tp, fp = _i32(to["to_procs"]), _i32(frm["from_procs"])
+    _chk(lib.b200_mat_create_mpiaij(int(m), int(m), int(host["N"]), _ip(sp["Ai"]), _ip(_i32(sp["Aj"])), _dp(_f64(sp["Aa"])),
+                                    int(g.size), _ip(sp["Bi"]), _ip(_i32(sp["Bj"])), _dp(_f64(sp["Ba"])), _ip(g),
+                                    int(to["nto"]), _ip(tp), _ip(ts), _ip(ti),
+                                    int(frm["nfrom"]), _ip(fp), _ip(fs), C.byref(h)), "MatAssemblyEnd_MPIAIJ (upload)")
+    return Mat(h, m, m)
+
+
+def comm_init(rank, size, dist=None, device=None):
+    """ncclCommInitRank for the library's own communicator; the id is broadcast with torch.distributed."""
+    import torch
+    import torch.distributed as td
+    dist = dist or td
+    buf = (C.c_ubyte * 128)()
+    if size > 1:
+        if rank == 0:
+            _chk(lib.b200_comm_get_unique_id(buf), "ncclGetUniqueId")
+        t = torch.tensor(list(bytes(buf)), dtype=torch.uint8, device=device or "cpu")
+        dist.broadcast(t, 0)
+        raw = bytes(t.cpu().numpy().tolist())
+        buf = (C.c_ubyte * 128).from_buffer_copy(raw)
+    _chk(lib.b200_comm_init(int(rank), int(size), buf), "b200_comm_init")

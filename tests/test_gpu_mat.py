@@ -1,0 +1,182 @@
+"""AIJ MatMult / MatMultAdd / MatGetDiagonal on the B200 against the reference's MatMult_SeqAIJ (oracle/_ref).
+Rows that go through the stream tiles are summed left to right like aij.h:384 -> BIT-EXACT; long rows (> 256
+entries) use a tree -> |dy_i| <= 1e-12 * sum_j |a_ij x_j| (the tolerance BASELINE.json states)."""
+import numpy as np
+import pytest
+
+from conftest import ex5_matrix
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(gpu, R, P, m, n, ip, j, a, seed=2, exact=True):
+    A = gpu.Mat.from_csr(m, n, ip, j, a)
+    ref = R.RefMat(m, n, ip, j, a, no_inode=True)
+    xh, yh = P.random_vector(n, seed), P.random_vector(m, seed + 1)
+    x, y, z = gpu.Vec(n, xh), gpu.Vec(m, yh), gpu.Vec(m)
+    A.mult(x, z)
+    zr = ref.mult(xh)
+    rows = np.repeat(np.arange(m), np.diff(ip))
+    scale = np.bincount(rows, weights=np.abs(a * xh[j]), minlength=m) if len(a) else np.zeros(m)
+    got = z.get_array()
+    if exact:
+        assert np.array_equal(got, zr)
+    assert np.all(np.abs(got - zr) <= 1e-12 * scale)
+    A.mult_add(x, y, z)
+    zr2 = ref.multadd(xh, yh)
+    got = z.get_array()
+    if exact:
+        assert np.array_equal(got, zr2)
+    assert np.all(np.abs(got - zr2) <= 1e-12 * (scale + np.abs(yh)))
+    A.mult_add(x, y, y)                                   # z aliases y (aij.c:1306)
+    assert np.array_equal(y.get_array(), got)
+    if m == n:
+        d = gpu.Vec(m)
+        A.get_diagonal(d)
+        assert np.array_equal(d.get_array(), ref.diagonal())
+    assert A.flops() == 2.0 * len(a) - np.count_nonzero(np.diff(ip))
+    return A
+
+
+def test_ex5_golden(gpu, goldens):
+    m, n, ip, j, a = ex5_matrix()
+    A = gpu.Mat.from_csr(m, n, ip, j, a)
+    x, y = gpu.Vec(n, np.arange(n, dtype=np.float64)), gpu.Vec(m)
+    A.mult(x, y)
+    assert [float("%G" % v) for v in y.get_array()] == goldens["mat_ex5_11_A"]["matmult"]
+    sq = [k for k in range(ip[-1]) if j[k] < m]
+    S = gpu.Mat.from_csr(m, m, np.arange(0, (m + 1) * m, m, dtype=np.int32), j[sq], a[sq])
+    d = gpu.Vec(m); S.get_diagonal(d)
+    assert [float("%G" % v) for v in d.get_array()] == goldens["mat_ex5_11_A"]["diagonal"]
+
+
+@pytest.mark.parametrize("case", ["lap2d_ex2", "lap7", "s27", "bs3", "rect", "empty_rows", "one_row", "no_rows", "all_empty"])
+def test_structured_bit_exact(gpu, R, P, case):
+    if case == "lap2d_ex2":
+        ip, j, a = P.laplace2d_5pt(57, 43); m = n = 57 * 43
+    elif case == "lap7":
+        ip, j, a = P.laplace3d_7pt(21); m = n = 21 ** 3
+    elif case == "s27":
+        ip, j, a = P.stencil3d_27pt(17); m = n = 17 ** 3
+    elif case == "bs3":
+        ip, j, a = P.elasticity_bs3(9); m = n = 3 * 9 ** 3
+    elif case == "rect":
+        m, n, ip, j, a = ex5_matrix()
+    elif case == "empty_rows":                            # ragged with many empty rows but below the compression ratio
+        ip0, j, a = P.laplace2d_5pt(30, 30)
+        keep = (np.arange(900) % 3) != 1
+        cnt = np.diff(ip0) * keep
+        sel = np.repeat(keep, np.diff(ip0))
+        ip, j, a, m, n = np.concatenate([[0], np.cumsum(cnt)]), j[sel], a[sel], 900, 900
+    elif case == "one_row":
+        ip, j, a, m, n = np.array([0, 3]), np.array([0, 2, 5], np.int32), np.array([1.5, -2.0, 0.25]), 1, 6
+    elif case == "no_rows":
+        ip, j, a, m, n = np.array([0]), np.zeros(0, np.int32), np.zeros(0), 0, 5
+    elif case == "all_empty":
+        ip, j, a, m, n = np.zeros(11, np.int64), np.zeros(0, np.int32), np.zeros(0), 10, 10
+    _check(gpu, R, P, m, n, np.asarray(ip, np.int64), np.asarray(j, np.int32), a)
+
+
+def test_compressed_rows_offdiag_like(gpu, R, P):
+    """A block that is mostly empty rows (the MPIAIJ off-diagonal block) is visited through the non-empty-row list."""
+    m, n = 5000, 300
+    rng = np.random.default_rng(5)
+    rows = np.sort(rng.choice(m, 400, replace=False))
+    cnt = np.zeros(m, np.int64); cnt[rows] = rng.integers(1, 9, rows.size)
+    ip = np.concatenate([[0], np.cumsum(cnt)])
+    j = np.concatenate([np.sort(rng.choice(n, c, replace=False)) for c in cnt[rows]]).astype(np.int32)
+    a = P.random_vector(j.size, 8)
+    A = _check(gpu, R, P, m, n, ip, j, a)
+    assert A.bin_info()["compressed"]
+
+
+def test_irregular_powerlaw(gpu, R, P):
+    """C4-like: power-law row lengths incl. rows far above the long-row threshold."""
+    N = 20000
+    ip, j, a = P.powerlaw(N, seed=4, xm=17.0, lmax=5000)
+    assert np.diff(ip).max() > 1000
+    A = _check(gpu, R, P, N, N, ip, j, a, exact=False)
+    info = A.bin_info()
+    assert info["nlong"] > 0 and info["ntiles"] > 0
+    # rows at or below the threshold are still bit-exact
+    ref = R.RefMat(N, N, ip, j, a)
+    xh = P.random_vector(N, 2)
+    x, y = gpu.Vec(N, xh), gpu.Vec(N)
+    A.mult(x, y)
+    short = np.diff(ip) <= 256
+    assert np.array_equal(y.get_array()[short], ref.mult(xh)[short])
+
+
+def test_deterministic_run_to_run(gpu, P):
+    ip, j, a = P.powerlaw(20000, seed=4, xm=17.0, lmax=5000)
+    A = gpu.Mat.from_csr(20000, 20000, ip, j, a)
+    x, y1, y2 = gpu.Vec(20000, P.random_vector(20000, 2)), gpu.Vec(20000), gpu.Vec(20000)
+    A.mult(x, y1); A.mult(x, y2)
+    assert np.array_equal(y1.get_array(), y2.get_array())
+    assert A.mult_dot(x, y1) == A.mult_dot(x, y2)
+
+
+def test_mult_dot_fused(gpu, R, P):
+    ip, j, a = P.laplace3d_7pt(30)
+    n = 27000
+    A = gpu.Mat.from_csr(n, n, ip, j, a)
+    xh = P.random_vector(n, 2)
+    x, y = gpu.Vec(n, xh), gpu.Vec(n)
+    d = A.mult_dot(x, y)
+    yr = R.RefMat(n, n, ip, j, a).mult(xh)
+    assert np.array_equal(y.get_array(), yr)
+    assert abs(d - R.vec_dot(xh, yr)) <= 1e-13 * np.abs(xh * yr).sum()
+
+
+def test_update_values_and_errors(gpu, R, P):
+    ip, j, a = P.laplace2d_5pt(20, 20)
+    A = gpu.Mat.from_csr(400, 400, ip, j, a)
+    A.update_values(2.0 * a)
+    xh = P.random_vector(400, 2)
+    x, y = gpu.Vec(400, xh), gpu.Vec(400)
+    A.mult(x, y)
+    assert np.array_equal(y.get_array(), R.RefMat(400, 400, ip, j, 2.0 * a).mult(xh))
+    with pytest.raises(gpu.PetscB200Error) as e:
+        A.mult(x, x)                                      # matrix.c:2143 "x and y must be different vectors"
+    assert e.value.code == 61
+
+
+def test_fixtures(gpu, P, fixtures):
+    ip, j, a = P.laplace3d_7pt(12)
+    N = 12 ** 3
+    A = gpu.Mat.from_csr(N, N, ip, j, a)
+    x, y, z = gpu.Vec(N, P.random_vector(N, 2)), gpu.Vec(N, P.random_vector(N, 3)), gpu.Vec(N)
+    A.mult(x, z); assert np.array_equal(z.get_array(), fixtures["lap7_12_mult"])
+    A.mult_add(x, y, z); assert np.array_equal(z.get_array(), fixtures["lap7_12_multadd"])
+    ip, j, a = P.powerlaw(3000, seed=4, xm=5.0, lmax=800)
+    A = gpu.Mat.from_csr(3000, 3000, ip, j, a)
+    x, z = gpu.Vec(3000, P.random_vector(3000, 5)), gpu.Vec(3000)
+    A.mult(x, z)
+    ref = fixtures["plaw3000_mult"]
+    assert np.all(np.abs(z.get_array() - ref) <= 1e-12 * np.maximum(np.abs(ref), 1.0))
+
+
+def test_full_size_c2_properties(gpu, P):
+    """BASELINE config 2 (7-point Laplacian on 256^3): size-independent properties.  A*1 is the exact row sum
+    (0 in the interior, 1..3 on faces/edges/corners), A is symmetric (x.Ay == y.Ax up to rounding), linearity."""
+    nx = 256
+    N = nx ** 3
+    ip, j, a = P.laplace3d_7pt(nx)
+    A = gpu.Mat.from_csr(N, N, ip, j, a)
+    one, y = gpu.Vec(N), gpu.Vec(N)
+    one.set(1.0)
+    A.mult(one, y)
+    rs = y.get_array()
+    g = np.arange(nx)
+    b1 = ((g == 0) | (g == nx - 1)).astype(np.float64)
+    expect = (b1[None, None, :] + b1[None, :, None] + b1[:, None, None]).reshape(-1)
+    assert np.array_equal(rs, expect)
+    xh, wh = P.random_vector(N, 2), P.random_vector(N, 3)
+    x, w, ax, aw = gpu.Vec(N, xh), gpu.Vec(N, wh), gpu.Vec(N), gpu.Vec(N)
+    A.mult(x, ax); A.mult(w, aw)
+    s1, s2 = w.dot(ax), x.dot(aw)
+    assert abs(s1 - s2) <= 1e-11 * N
+    x.axpy(2.0, w)                                         # A(x + 2w) == Ax + 2Aw up to rounding
+    A.mult(x, y)
+    ax.axpy(2.0, aw); ax.axpy(-1.0, y)
+    assert ax.norm(gpu.NORM_INFINITY) <= 1e-12 * 12 * 3

@@ -1,0 +1,48 @@
+"""The MPIAIJ operator's device kernels (diagonal block, compressed off-diagonal block added from the result) with
+P virtual ranks emulated in one process on one GPU: the test plays the scatter (lvec = x[garray], a pure copy), the
+library does diag-mult + offdiag-multadd, and the result is compared with the reference's MatMult_SeqAIJ +
+MatMultAdd_SeqAIJ pair per rank (oracle/mpiaij_restate.mult) — bit-exact for the stencil cases."""
+import importlib
+
+import numpy as np
+import pytest
+
+from test_mpiaij_host import _gens, serial_plans
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name,size", [("lap7", 2), ("lap7", 8), ("s27", 4), ("bs3", 3), ("plaw", 4), ("lap2d", 1)])
+def test_virtual_ranks(gpu, R, P, name, size):
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    from oracle import mpiaij_restate as O
+    N, bs, gen = _gens(P)[name]
+    ranges, host = serial_plans(par, size, N, gen, bs)
+    def gen0(r0, r1):
+        ai, aj, aa = gen(r0, r1)
+        return ai - ai[0], aj, aa
+    _, S = O.all_structures(size, N, gen0, bs)
+    xh, yh = P.random_vector(N, 2), P.random_vector(N, 3)
+    want = O.mult(R, ranges, S, xh)
+    want_add = O.mult(R, ranges, S, xh, add_y=yh)
+    got, got_add = np.empty(N), np.empty(N)
+    for r in range(size):
+        rs, re_ = int(ranges[r]), int(ranges[r + 1])
+        h = dict(host[r], m=re_ - rs, N=N)
+        A = par.create_mpiaij(h)
+        g = h["split"]["garray"]
+        x, y, z = gpu.Vec(re_ - rs, xh[rs:re_]), gpu.Vec(re_ - rs, yh[rs:re_]), gpu.Vec(re_ - rs)
+        lv = gpu.Vec(max(g.size, 1), xh[g] if g.size else np.zeros(1))
+        gpu._chk(gpu.lib.b200_mat_mpiaij_set_lvec(A.h, lv.p), "set_lvec")
+        A.mult(x, z)
+        got[rs:re_] = z.get_array()
+        A.mult_add(x, y, z)
+        got_add[rs:re_] = z.get_array()
+        if size > 1 and name != "plaw":
+            assert A.nnz() == h["split"]["Aj"].size + h["split"]["Bj"].size
+    if name == "plaw":
+        sc = np.maximum(np.abs(want), 1.0)
+        assert np.all(np.abs(got - want) <= 1e-12 * sc) and np.all(np.abs(got_add - want_add) <= 1e-12 * (sc + np.abs(yh)))
+    else:
+        assert np.array_equal(got, want)
+        assert np.array_equal(got_add, want_add)
