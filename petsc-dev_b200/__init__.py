@@ -314,3 +314,10 @@ def ksp_solve(A, b, x, histmax=None, **kw):
     res = KSPResult()
     _chk(lib.b200_ksp_solve(A.h, C.byref(o), b.p, x.p, _dp(hist), histmax, C.byref(res)), "KSPSolve")
     return dict(its=res.its, reason=res.reason, history=hist[:res.nhist].copy(), rnorm=res.rnorm, solve_ms=res.solve_ms)
+
+
+def pinned_array(n):
+    """n doubles of page-locked host memory as a numpy array (for the end-to-end path's H2D/D2H copies)."""
+    p = C.c_void_p()
+    _chk(lib.b200_host_alloc(C.c_size_t(8 * max(int(n), 1)), C.byref(p)), "cudaHostAlloc")
+    return np.ctypeslib.as_array(C.cast(p, c_dp), shape=(int(n),))
