@@ -9,9 +9,20 @@ from conftest import monitor_short, tridiag
 pytestmark = pytest.mark.gpu
 
 
-def _hist_dev(h, hr):
+def _hist_dev(h, hr, window=1e-5):
+    """Deviation of a residual history from the reference's: the larger of
+         max_k |h_k - hr_k| / hr_k   over the entries with hr_k >= window * hr_0   (relative, BASELINE's 1e-10), and
+         max_k |h_k - hr_k| / hr_0   over ALL entries (rounding in a Krylov recurrence is absolute in ||r_0||:
+                                     once the residual has dropped by 1e5 a 1e-16 perturbation of a dot product is
+                                     already 1e-11 relative to r_k, for the reference against itself with another
+                                     BLAS as much as for us; see DESIGN.md "KSP tolerances")."""
     k = min(len(h), len(hr))
-    return np.max(np.abs(h[:k] - hr[:k]) / hr[:k]) if k else 0.0
+    if not k:
+        return 0.0
+    h, hr = np.asarray(h[:k]), np.asarray(hr[:k])
+    d = np.abs(h - hr)
+    win = hr >= window * hr[0]
+    return max(np.max(d[win] / hr[win]) if win.any() else 0.0, np.max(d) / hr[0])
 
 
 def _solve_both(gpu, R, ip, j, a, n, bh, ksp, pc, rtol=1e-8, tol=1e-10, **kw):
