@@ -145,6 +145,11 @@ int b200_mat_get_diagonal(b200_mat A, double *d);                             /*
 int b200_mat_flops(b200_mat A, double *mult_flops);                           /* 2*nz - nonzerorow, aij.c:1281                                 */
 int b200_mat_bytes(b200_mat A, double *mult_bytes);                           /* algorithmic bytes of one MatMult                  */
 int b200_mat_bin_info(b200_mat A, int *ntiles, int *nlong, int *compressed);  /* row-binning summary                                           */
+int b200_mat_bin_info2(b200_mat A, int *lanes_per_row, int *long_thresh, int *grid, int *shape, int *park); /* tile-kernel launch description */
+/* Row-binning policy for matrices created AFTER the call (-1 = automatic): launch shape index, lanes per row
+ * (1, 2, 4, ... 32; 1 = every tile row is summed left to right exactly like aij.h:384-386), long-row threshold,
+ * and whether products are parked in shared memory before the row sums (the choice for irregular row lengths). */
+int b200_spmv_set_tuning(int shape, int lanes_per_row, int long_thresh, int park);
 /* the four fused entry points the CG driver uses (kept public so a KSP plugin can call them) */
 int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double *xdoty_host);   /* y = A x and x.y in one pass (seq, m == n)      */
 

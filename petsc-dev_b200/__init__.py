@@ -290,7 +290,16 @@ class Mat:
     def bin_info(self):
         a, b, c = C.c_int(), C.c_int(), C.c_int()
         _chk(lib.b200_mat_bin_info(self.h, C.byref(a), C.byref(b), C.byref(c)), "bin_info")
-        return dict(ntiles=a.value, nlong=b.value, compressed=bool(c.value))
+        g, lt, gr, sh, pk = C.c_int(), C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        _chk(lib.b200_mat_bin_info2(self.h, C.byref(g), C.byref(lt), C.byref(gr), C.byref(sh), C.byref(pk)), "bin_info2")
+        return dict(ntiles=a.value, nlong=b.value, compressed=bool(c.value), lanes_per_row=g.value,
+                    long_thresh=lt.value, grid=gr.value, shape=sh.value, park=bool(pk.value))
+
+
+def spmv_tuning(shape=-1, lanes_per_row=-1, long_thresh=-1, park=-1):
+    """Row-binning policy for matrices created after the call (-1 = automatic); lanes_per_row=1 makes every tile row
+    a left-to-right sum, bit-identical to MatMult_SeqAIJ."""
+    _chk(lib.b200_spmv_set_tuning(int(shape), int(lanes_per_row), int(long_thresh), int(park)), "spmv_tuning")
 
 
 def ksp_options(**kw):

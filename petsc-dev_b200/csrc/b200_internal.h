@@ -64,11 +64,17 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
   int        ncrows;          /* rows in the visiting order (m, or the number of non-empty rows)                     */
   int       *d_ci;            /* [ncrows+1] offsets in visiting order (== d_i when not compressed)                   */
   int       *d_rindex;        /* [ncrows] visiting order -> row id (NULL when not compressed)                        */
-  int        ntiles;          /* stream tiles: contiguous runs of short rows, <= TILE_NNZ entries each               */
+  int        cfg, G, grid;    /* tile-kernel launch shape, lanes per row (1..32), persistent grid size               */
+  int        long_thresh;     /* rows longer than this go to the long-row kernel                                     */
+  int        ntiles;          /* row tiles: contiguous runs of rows, <= tile_nnz entries and <= threads/G rows each  */
   int4      *d_tiles;         /* {row_begin, row_end, k_begin, k_end} in visiting order                              */
-  int        nlong;           /* rows longer than LONG_THRESH, one CTA each                                          */
+  int        park;            /* 1: products are parked in shared memory before the row sums (irregular matrices)    */
+  int        nlong;           /* rows longer than long_thresh: cut into chunk tiles                                   */
+  int        nchunks;
   int       *d_long;          /* their positions in visiting order                                                   */
-  double    *d_dotpart;       /* [ntiles + nlong] per-CTA partials of the fused x.y                                  */
+  int       *d_longstart;     /* [nlong+1] first chunk slot of each long row                                          */
+  double    *d_longpart;      /* [nchunks] per-chunk partial sums                                                     */
+  double    *d_dotpart;       /* [grid + nlong] per-CTA partials of the fused x.y                                    */
 };
 
 struct b200_mat_s {

@@ -4,12 +4,11 @@
  * MatMult_SeqAIJCUSP (src/mat/impls/aij/seq/seqcusp/aijcusp.cu:349-390).
  *
  * Row binning (done once at upload, the device analogue of MatAssemblyEnd_SeqAIJ's compressed-row/inode checks):
- *   - "stream tiles": maximal runs of consecutive short rows holding <= TILE_NNZ entries.  One CTA per tile: the
- *     tile's values and column ids are streamed with 128-bit loads, multiplied by the gathered x (read-only path,
- *     L1/L2 resident) and parked in shared memory; then one thread per row adds its products LEFT TO RIGHT starting
- *     from 0 (MatMult) or y[i] (MatMultAdd) — the reference's exact association (aij.h:384-386), so with -fmad=false
- *     these rows are bit-identical to the CPU result.  Row offsets of the tile are staged in shared memory.
- *   - "long rows" (> LONG_THRESH entries): one CTA per row, strided loads, fixed-shape tree reduction
+ *   - "row tiles": maximal runs of consecutive rows holding <= tile_nnz entries and <= threads/G rows, walked by the
+ *     persistent TMA-fed tile kernel (b200_spmv_kernels.cuh).  G lanes per row, chosen from the mean row length: G = 1
+ *     (short rows, e.g. the 5/7-point stencils) sums each row left to right exactly like the reference, so with
+ *     -fmad=false those rows are bit-identical to the CPU result; G > 1 uses a fixed shuffle tree.
+ *   - "long rows" (> long_thresh entries): one CTA per row, strided loads, fixed-shape tree reduction
  *     (deterministic; differs from the reference in association only).
  *   - blocks that are mostly empty rows (the MPIAIJ off-diagonal block) are visited through the list of non-empty
  *     rows only (what Mat_CompressedRow does on the CPU: src/mat/utils/compressedrow.c:28-80).
@@ -17,125 +16,26 @@
  */
 #include "b200_internal.h"
 #include <vector>
+#include <math.h>
 
-#define SPMV_THREADS 256
-#define TILE_NNZ     2048
-#define TILE_ROWS    512
-#define LONG_THRESH  256
-#define LONG_THREADS 128
-#define TILE_GROUPS  (TILE_NNZ / 4 + 1)                               /* 16-byte groups a tile can touch          */
-#define TILE_ITERS   ((TILE_GROUPS + SPMV_THREADS - 1) / SPMV_THREADS)
+#include "b200_spmv_kernels.cuh"
 
-template <bool ADD, bool DOT>
-__global__ void __launch_bounds__(SPMV_THREADS)
-spmv_stream_kernel(const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
-                   const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
-                   const double *yin, double *z, double *__restrict__ dotpart)
-{
-  __shared__ double s_prod[TILE_NNZ];
-  __shared__ int    s_rp[TILE_ROWS + 1];
-  __shared__ double s_red[SPMV_THREADS / 32];
-  const int4 t  = __ldg(&tiles[blockIdx.x]);
-  const int  rb = t.x, nrows = t.y - t.x, k0 = t.z, k1 = t.w;
-  const int  tid = threadIdx.x;
 
-  /* stage the tile's row offsets (relative to k0) */
-  for (int r = tid; r <= nrows; r += SPMV_THREADS) s_rp[r] = __ldg(&ci[rb + r]) - k0;
-
-  /* phase 1: stream a/j in aligned 16-byte groups, gather x, park the products */
-  const int g0 = k0 >> 2, g1 = (k1 + 3) >> 2;
-  int4    jv[TILE_ITERS];
-  double2 av[TILE_ITERS][2];
-#pragma unroll
-  for (int it = 0; it < TILE_ITERS; it++) {
-    const int g = g0 + tid + it * SPMV_THREADS;
-    if (g < g1) {
-      jv[it]    = __ldcs(reinterpret_cast<const int4 *>(aj) + g);
-      av[it][0] = __ldcs(reinterpret_cast<const double2 *>(aa) + 2 * (size_t)g);
-      av[it][1] = __ldcs(reinterpret_cast<const double2 *>(aa) + 2 * (size_t)g + 1);
-    }
-  }
-#pragma unroll
-  for (int it = 0; it < TILE_ITERS; it++) {
-    const int g = g0 + tid + it * SPMV_THREADS;
-    if (g < g1) {
-      const int k = 4 * g - k0;                          /* position of the group's first entry in the tile */
-      const int n1 = k1 - k0;
-      if (k >= 0 && k + 3 < n1) {
-        const double p0 = av[it][0].x * __ldg(&x[jv[it].x]);
-        const double p1 = av[it][0].y * __ldg(&x[jv[it].y]);
-        const double p2 = av[it][1].x * __ldg(&x[jv[it].z]);
-        const double p3 = av[it][1].y * __ldg(&x[jv[it].w]);
-        s_prod[k] = p0; s_prod[k + 1] = p1; s_prod[k + 2] = p2; s_prod[k + 3] = p3;
-      } else {
-        if (k     >= 0 && k     < n1) s_prod[k]     = av[it][0].x * __ldg(&x[jv[it].x]);
-        if (k + 1 >= 0 && k + 1 < n1) s_prod[k + 1] = av[it][0].y * __ldg(&x[jv[it].y]);
-        if (k + 2 >= 0 && k + 2 < n1) s_prod[k + 2] = av[it][1].x * __ldg(&x[jv[it].z]);
-        if (k + 3 >= 0 && k + 3 < n1) s_prod[k + 3] = av[it][1].y * __ldg(&x[jv[it].w]);
-      }
-    }
-  }
-  __syncthreads();
-
-  /* phase 2: one thread per row, left-to-right sum */
-  double dot = 0.0;
-  for (int r = tid; r < nrows; r += SPMV_THREADS) {
-    const int row = rindex ? __ldg(&rindex[rb + r]) : rb + r;
-    const int b = s_rp[r], e = s_rp[r + 1];
-    double sum = ADD ? yin[row] : 0.0;
-    for (int k = b; k < e; k++) sum += s_prod[k];
-    z[row] = sum;
-    if (DOT) dot += __ldg(&x[row]) * sum;
-  }
-  if (DOT) {
-    const int lane = tid & 31, wid = tid >> 5;
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-    if (lane == 0) s_red[wid] = dot;
-    __syncthreads();
-    if (wid == 0) {
-      double v = (lane < SPMV_THREADS / 32) ? s_red[lane] : 0.0;
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0) dotpart[blockIdx.x] = v;
-    }
-  }
-}
-
-/* one CTA per long row */
-template <bool ADD, bool DOT>
-__global__ void __launch_bounds__(LONG_THREADS)
-spmv_long_kernel(const int *__restrict__ longrows, const int *__restrict__ ci, const int *__restrict__ rindex,
-                 const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
-                 const double *yin, double *z, double *__restrict__ dotpart)
-{
-  __shared__ double s_red[LONG_THREADS / 32];
-  const int r = __ldg(&longrows[blockIdx.x]);
-  const int row = rindex ? __ldg(&rindex[r]) : r;
-  const int k0 = __ldg(&ci[r]), k1 = __ldg(&ci[r + 1]);
-  double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
-  int k = k0 + threadIdx.x;
-  for (; k + 3 * LONG_THREADS < k1; k += 4 * LONG_THREADS) {
-    const int j0 = __ldcs(&aj[k]), j1 = __ldcs(&aj[k + LONG_THREADS]), j2 = __ldcs(&aj[k + 2 * LONG_THREADS]), j3 = __ldcs(&aj[k + 3 * LONG_THREADS]);
-    const double a0 = __ldcs(&aa[k]), a1 = __ldcs(&aa[k + LONG_THREADS]), a2 = __ldcs(&aa[k + 2 * LONG_THREADS]), a3 = __ldcs(&aa[k + 3 * LONG_THREADS]);
-    s0 += a0 * __ldg(&x[j0]); s1 += a1 * __ldg(&x[j1]); s2 += a2 * __ldg(&x[j2]); s3 += a3 * __ldg(&x[j3]);
-  }
-  for (; k < k1; k += LONG_THREADS) s0 += __ldcs(&aa[k]) * __ldg(&x[__ldcs(&aj[k])]);
-  double s = (s0 + s1) + (s2 + s3);
-  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-  if (lane == 0) s_red[wid] = s;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    double v = 0.0;
-#pragma unroll
-    for (int w = 0; w < LONG_THREADS / 32; w++) v += s_red[w];
-    const double out = ADD ? yin[row] + v : v;
-    z[row] = out;
-    if (DOT) dotpart[blockIdx.x] = __ldg(&x[row]) * out;
-  }
-}
+/* launch shapes of the tile kernel; the active one is chosen at upload (default 0, B200_SPMV_CFG overrides — a tuning
+ * aid, every shape computes the same numbers) */
+struct SpmvCfg { int threads, tile_nnz, stages, ctas_per_sm; };
+static const SpmvCfg g_cfgs[] = {
+  {256, 2048, 1, 8},      /* default: 2048 resident lanes per SM; 8 single-stage CTAs overlap each other's loads     */
+  {256, 2048, 2, 4},
+  {512, 4096, 2, 2},
+  {128, 1024, 1, 16},
+  {512, 4096, 1, 4},
+  {256, 1792, 2, 5},
+  {256, 4096, 2, 2},
+  {384, 3072, 1, 5},
+};
+#define SPMV_NCFG ((int)(sizeof(g_cfgs) / sizeof(g_cfgs[0])))
+static int g_tune_cfg = -1, g_tune_G = -1, g_tune_long = -1, g_tune_park = -1;
 
 /* deterministic final pass over the per-CTA partials of the fused dot */
 __global__ void __launch_bounds__(1024) dot_final_kernel(int n, const double *__restrict__ part, double *out)
@@ -187,7 +87,7 @@ void b200_seq_free(B200Seq *S)
   if (!S) return;
   if (S->d_ci && S->d_ci != S->d_i) cudaFree(S->d_ci);
   cudaFree(S->d_i); cudaFree(S->d_j); cudaFree(S->d_a); cudaFree(S->d_rindex);
-  cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_dotpart);
+  cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
   memset(S, 0, sizeof(*S));
 }
 
@@ -220,19 +120,63 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
     vi = ci.data(); nrows = nonempty;
   }
   S->ncrows = nrows;
-  /* binning */
+  /* lanes per row from the mean length of the non-empty rows (B200_SPMV_G forces a value: 1 = reference order) */
+  {
+    int cfg = 0;
+    const char *ec = getenv("B200_SPMV_CFG");
+    if (ec && atoi(ec) >= 0 && atoi(ec) < SPMV_NCFG) cfg = atoi(ec);
+    if (g_tune_cfg >= 0 && g_tune_cfg < SPMV_NCFG) cfg = g_tune_cfg;
+    S->cfg = cfg;
+    /* statistics of the non-empty rows: mean and coefficient of variation of the lengths */
+    const double mean = nonempty ? (double)nz / (double)nonempty : 0.0;
+    double ss = 0.0;
+    for (int r = 0; r < m; r++) { const double l = (double)(i[r + 1] - i[r]); if (l > 0) ss += (l - mean) * (l - mean); }
+    const double cv = (nonempty && mean > 0) ? sqrt(ss / (double)nonempty) / mean : 0.0;
+    /* lanes per row: one lane (reference summation order) up to 32 entries per row, else about 8-16 entries per lane */
+    int G = 1;
+    if (mean > 32.0) while (G < 32 && mean >= 16.0 * G) G *= 2;
+    const char *eg = getenv("B200_SPMV_G");
+    if (eg) { const int v = atoi(eg); if (v == 1 || v == 2 || v == 4 || v == 8 || v == 16 || v == 32) G = v; }
+    if (g_tune_G > 0) G = g_tune_G;
+    S->G = G;
+    S->park = cv > 0.5;
+    const char *ep = getenv("B200_SPMV_PARK");
+    if (ep) S->park = atoi(ep) != 0;
+    if (g_tune_park >= 0) S->park = g_tune_park != 0;
+    S->long_thresh = g_cfgs[cfg].tile_nnz < 64 * G ? g_cfgs[cfg].tile_nnz : 64 * G;
+    if (S->long_thresh < 256) S->long_thresh = 256 < g_cfgs[cfg].tile_nnz ? 256 : g_cfgs[cfg].tile_nnz;
+    const char *el = getenv("B200_SPMV_LONG");
+    if (el && atoi(el) > 0 && atoi(el) <= g_cfgs[cfg].tile_nnz) S->long_thresh = atoi(el);
+    if (g_tune_long > 0 && g_tune_long <= g_cfgs[cfg].tile_nnz) S->long_thresh = g_tune_long;
+  }
+  const int tile_nnz = g_cfgs[S->cfg].tile_nnz, tile_rows = g_cfgs[S->cfg].threads / S->G;
+  /* binning: row tiles, and chunk tiles {row position, -(slot+1), k_begin, k_end} for the long rows */
   std::vector<int4> tiles;
-  std::vector<int>  longrows;
-  int ts = 0;
+  std::vector<int>  longrows, longstart;
+  int ts = 0, nchunks = 0;
   auto close_tile = [&](int re) { if (re > ts) tiles.push_back(make_int4(ts, re, vi[ts], vi[re])); };
   for (int r = 0; r < nrows; r++) {
     const int len = vi[r + 1] - vi[r];
-    if (len > LONG_THRESH) { close_tile(r); longrows.push_back(r); ts = r + 1; continue; }
-    if (vi[r + 1] - vi[ts] > TILE_NNZ || r - ts >= TILE_ROWS) { close_tile(r); ts = r; }
+    if (len > S->long_thresh) {
+      close_tile(r);
+      longrows.push_back(r); longstart.push_back(nchunks);
+      for (int kb = vi[r]; kb < vi[r + 1]; kb += tile_nnz) {
+        const int ke = kb + tile_nnz < vi[r + 1] ? kb + tile_nnz : vi[r + 1];
+        tiles.push_back(make_int4(r, -(nchunks + 1), kb, ke));
+        nchunks++;
+      }
+      ts = r + 1;
+      continue;
+    }
+    if (vi[r + 1] - vi[ts] > tile_nnz || r - ts >= tile_rows) { close_tile(r); ts = r; }
   }
   close_tile(nrows);
+  longstart.push_back(nchunks);
+  S->nchunks = nchunks;
   S->ntiles = (int)tiles.size();
   S->nlong  = (int)longrows.size();
+  S->grid   = g_b200.nsm * g_cfgs[S->cfg].ctas_per_sm;
+  if (S->grid > S->ntiles) S->grid = S->ntiles;
 
   const size_t pad = 8;
   B200_CUDA(cudaMalloc((void **)&S->d_i, sizeof(int) * ((size_t)m + 1)));
@@ -260,9 +204,63 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
   if (S->nlong) {
     B200_CUDA(cudaMalloc((void **)&S->d_long, sizeof(int) * longrows.size()));
     B200_CUDA(cudaMemcpy(S->d_long, longrows.data(), sizeof(int) * longrows.size(), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMalloc((void **)&S->d_longstart, sizeof(int) * longstart.size()));
+    B200_CUDA(cudaMemcpy(S->d_longstart, longstart.data(), sizeof(int) * longstart.size(), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMalloc((void **)&S->d_longpart, sizeof(double) * (size_t)nchunks));
   }
-  B200_CUDA(cudaMalloc((void **)&S->d_dotpart, sizeof(double) * ((size_t)S->ntiles + S->nlong + 1)));
+  B200_CUDA(cudaMalloc((void **)&S->d_dotpart, sizeof(double) * ((size_t)S->grid + S->nlong + 1)));
   return 0;
+}
+
+/* ---- tile-kernel dispatch: (launch shape) x (lanes per row) x (add, dot) */
+template <int G, bool PARK, int THREADS, int TILE_NNZ, int STAGES>
+static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+{
+  const size_t smem = SpmvSmem<THREADS, TILE_NNZ, STAGES>::BYTES;
+#define GO(ADD, DOT) do { \
+    auto kern = spmv_tile_kernel<G, PARK, ADD, DOT, THREADS, TILE_NNZ, STAGES>; \
+    static bool attr_done = false; \
+    if (!attr_done) { cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; attr_done = true; } \
+    kern<<<S->grid, THREADS, smem, st>>>(S->ntiles, S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart, S->d_longpart); \
+  } while (0)
+  if (add) { if (dot) GO(true, true); else GO(true, false); }
+  else     { if (dot) GO(false, true); else GO(false, false); }
+#undef GO
+  return cudaGetLastError();
+}
+
+template <int G, int THREADS, int TILE_NNZ, int STAGES>
+static cudaError_t launch_tile4(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+{
+  return S->park ? launch_tile5<G, true, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st)
+                 : launch_tile5<G, false, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+}
+
+template <int THREADS, int TILE_NNZ, int STAGES>
+static cudaError_t launch_tile3(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+{
+  switch (S->G) {
+    case 1:  return launch_tile4<1,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    case 2:  return launch_tile4<2,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    case 4:  return launch_tile4<4,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    case 8:  return launch_tile4<8,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    case 16: return launch_tile4<16, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    default: return launch_tile4<32, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+  }
+}
+
+static cudaError_t launch_tile(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+{
+  switch (S->cfg) {                       /* must mirror g_cfgs[] */
+    case 0:  return launch_tile3<256, 2048, 1>(S, add, dot, x, yin, z, st);
+    case 1:  return launch_tile3<256, 2048, 2>(S, add, dot, x, yin, z, st);
+    case 2:  return launch_tile3<512, 4096, 2>(S, add, dot, x, yin, z, st);
+    case 3:  return launch_tile3<128, 1024, 1>(S, add, dot, x, yin, z, st);
+    case 4:  return launch_tile3<512, 4096, 1>(S, add, dot, x, yin, z, st);
+    case 5:  return launch_tile3<256, 1792, 2>(S, add, dot, x, yin, z, st);
+    case 6:  return launch_tile3<256, 4096, 2>(S, add, dot, x, yin, z, st);
+    default: return launch_tile3<384, 3072, 1>(S, add, dot, x, yin, z, st);
+  }
 }
 
 /* z = (add ? yin : 0) + S x ; dot_out (device scalar) receives x.z when non-NULL (needs m == n, all rows visited) */
@@ -279,15 +277,21 @@ int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *
     B200_LAUNCHED(1);
   }
   if (dot_out && S->compressed) return b200_seterr(B200_ERR_SUP, "fused dot needs an uncompressed square block");
-#define SPMV_GO(ADD, DOT) do { \
-    if (S->ntiles) { spmv_stream_kernel<ADD, DOT><<<S->ntiles, SPMV_THREADS, 0, st>>>(S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart); B200_LAUNCHED(1); } \
-    if (S->nlong)  { spmv_long_kernel<ADD, DOT><<<S->nlong, LONG_THREADS, 0, st>>>(S->d_long, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart + S->ntiles); B200_LAUNCHED(1); } \
-  } while (0)
-  if (add) { if (dot_out) SPMV_GO(true, true); else SPMV_GO(true, false); }
-  else     { if (dot_out) SPMV_GO(false, true); else SPMV_GO(false, false); }
-#undef SPMV_GO
+  if (S->ntiles) {
+    B200_CUDA(launch_tile(S, add, dot_out != NULL, x, yin, z, st));
+    B200_LAUNCHED(1);
+  }
+  if (S->nlong) {
+    double *dp = S->d_dotpart + S->grid;
+    const int fg = (S->nlong + 127) / 128;
+#define FIN(ADD, DOT) spmv_long_finish_kernel<ADD, DOT><<<fg, 128, 0, st>>>(S->nlong, S->d_long, S->d_longstart, S->d_rindex, S->d_longpart, x, yin, z, dp)
+    if (add) { if (dot_out) FIN(true, true); else FIN(true, false); }
+    else     { if (dot_out) FIN(false, true); else FIN(false, false); }
+#undef FIN
+    B200_LAUNCHED(1);
+  }
   if (dot_out) {
-    dot_final_kernel<<<1, 1024, 0, st>>>(S->ntiles + S->nlong, S->d_dotpart, dot_out);
+    dot_final_kernel<<<1, 1024, 0, st>>>(S->grid + S->nlong, S->d_dotpart, dot_out);
     B200_LAUNCHED(1);
   }
   return 0;
@@ -351,6 +355,25 @@ extern "C" int b200_mat_bin_info(b200_mat A, int *ntiles, int *nlong, int *compr
   if (ntiles) *ntiles = S->ntiles;
   if (nlong) *nlong = S->nlong;
   if (compressed) *compressed = S->compressed;
+  return 0;
+}
+
+extern "C" int b200_mat_bin_info2(b200_mat A, int *lanes, int *long_thresh, int *grid, int *shape, int *park)
+{
+  if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null matrix");
+  if (lanes) *lanes = A->A.G;
+  if (long_thresh) *long_thresh = A->A.long_thresh;
+  if (grid) *grid = A->A.grid;
+  if (shape) *shape = A->A.cfg;
+  if (park) *park = A->A.park;
+  return 0;
+}
+
+extern "C" int b200_spmv_set_tuning(int shape, int lanes, int long_thresh, int park)
+{
+  if (shape >= SPMV_NCFG) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "launch shape %d out of range (0..%d)", shape, SPMV_NCFG - 1);
+  if (lanes > 0 && (lanes > 32 || (lanes & (lanes - 1)))) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "lanes per row must be a power of two <= 32");
+  g_tune_cfg = shape; g_tune_G = lanes; g_tune_long = long_thresh; g_tune_park = park;
   return 0;
 }
 

@@ -1,0 +1,253 @@
+/* b200_spmv_kernels.cuh — the sm_100a CSR SpMV kernels (device code only; hosts: b200_spmv.cu, tools/).
+ *
+ * spmv_tile_kernel: persistent CTAs walk "row tiles" (contiguous runs of rows, <= TILE_NNZ entries, <= THREADS/G rows).
+ *   - the tile's values and column ids are brought into shared memory by the TMA engine (1-D cp.async.bulk, completion
+ *     on an mbarrier, L2 evict-first policy so the matrix stream does not push x out of L2), STAGES tiles deep, so the
+ *     HBM stream is continuous and never touches the LSU/L1 data pipe (ncu on the first version of this kernel showed
+ *     that pipe, not DRAM, was the limiter: 69 % l1tex wavefronts at 53 % of HBM peak);
+ *   - G lanes own one row.  G = 1: the lane walks its row LEFT TO RIGHT starting from 0 (MatMult) or y[i] (MatMultAdd) —
+ *     the reference's association exactly (PetscSparseDensePlusDot, src/mat/impls/aij/seq/aij.h:384-386; aij.c:1338),
+ *     so with -fmad=false the result is bit-identical to MatMult_SeqAIJ.  Consecutive lanes own consecutive rows: the
+ *     x gathers of a warp are (for banded matrices) one contiguous 256-byte run, the shared-memory reads are strided by
+ *     the row length (conflict-free for odd lengths).  G > 1: lanes stride the row, fixed xor-shuffle tree at the end
+ *     (deterministic; association differs from the reference, well inside the 1e-12 bound);
+ *   - row offsets / y of the NEXT tile and the tile descriptor after it are prefetched into registers while the
+ *     current tile is computed.
+ *   - PARK variant (irregular matrices): a first pass in which the lanes stride the tile's ENTRIES (perfectly balanced,
+ *     8 independent x gathers in flight per lane) parks the products in shared memory; the row sums then only read
+ *     shared memory, so a long row in the tile delays its lanes by LDS+DADD latencies, not by L2 gathers;
+ *   - rows longer than the threshold are cut into chunks of one tile each (descriptor .y = -(slot+1)); the whole CTA
+ *     strides a chunk and leaves one partial per chunk; spmv_long_finish_kernel adds a row's partials in chunk order.
+ *     The chunks travel through the same TMA pipeline and are dealt round-robin to the CTAs like any other tile. */
+#ifndef B200_SPMV_KERNELS_CUH
+#define B200_SPMV_KERNELS_CUH
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define SPMV_ALIGN_PAD 8      /* entries of slack per stage: the bulk copies start/end on 4-entry boundaries */
+
+__device__ __forceinline__ uint32_t b200_smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void b200_mbar_init(uint64_t *bar, int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(b200_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void b200_mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b200_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void b200_mbar_wait(uint64_t *bar, uint32_t parity)
+{
+  asm volatile("{\n"
+               ".reg .pred P1;\n"
+               "LAB_WAIT:\n"
+               "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+               "@P1 bra DONE;\n"
+               "bra LAB_WAIT;\n"
+               "DONE:\n"
+               "}" ::"r"(b200_smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ uint64_t b200_policy_evict_first()
+{
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+/* 1-D TMA bulk copy global -> shared; bytes % 16 == 0, both addresses 16-byte aligned */
+__device__ __forceinline__ void b200_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar, uint64_t pol)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], [%1], %2, [%3], %4;"
+               ::"r"(b200_smem_u32(dst)), "l"(src), "r"(bytes), "r"(b200_smem_u32(bar)), "l"(pol) : "memory");
+}
+
+template <int THREADS, int TILE_NNZ, int STAGES>
+struct SpmvSmem {
+  static constexpr int    STAGE_ELEMS = TILE_NNZ + SPMV_ALIGN_PAD;
+  static constexpr size_t BYTES = (size_t)STAGES * STAGE_ELEMS * 12 + STAGES * 8 + 64;
+};
+
+/* tiles[t] = {row_begin, row_end, k_begin, k_end} in visiting order (ci = offsets in visiting order; rindex maps a
+ * visiting position to the row id when the block is stored compressed, else NULL). */
+template <int G, bool PARK, bool ADD, bool DOT, int THREADS, int TILE_NNZ, int STAGES>
+__global__ void __launch_bounds__(THREADS)
+spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
+                 const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
+                 const double *yin, double *z, double *__restrict__ dotpart, double *__restrict__ longpart)
+{
+  constexpr int SE = TILE_NNZ + SPMV_ALIGN_PAD;
+  extern __shared__ __align__(128) unsigned char spmv_smem[];
+  double   *s_a  = reinterpret_cast<double *>(spmv_smem);
+  int      *s_j  = reinterpret_cast<int *>(spmv_smem + (size_t)STAGES * SE * 8);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(spmv_smem + (size_t)STAGES * SE * 12);
+  __shared__ double s_red[THREADS / 32];
+
+  const int tid = threadIdx.x, r = tid / G, g = tid % G;
+  const int stride = gridDim.x;
+  int t = blockIdx.x;
+  uint64_t pol = 0;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) b200_mbar_init(&bars[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    pol = b200_policy_evict_first();
+  }
+  __syncthreads();
+
+  auto issue = [&](int s, int4 d) {                 /* thread 0 only */
+    const int ka = d.z & ~3, kb = (d.w + 3) & ~3;
+    const uint32_t n = (uint32_t)(kb - ka);
+    if (n == 0) { b200_mbar_expect_tx(&bars[s], 0); return; }
+    b200_mbar_expect_tx(&bars[s], n * 12u);
+    b200_bulk_g2s(s_a + (size_t)s * SE, aa + ka, n * 8u, &bars[s], pol);
+    b200_bulk_g2s(s_j + (size_t)s * SE, aj + ka, n * 4u, &bars[s], pol);
+  };
+
+  /* prologue: fill the pipeline */
+  if (tid == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; s++) {
+      const int tt = t + s * stride;
+      if (tt < ntiles) issue(s, __ldg(&tiles[tt]));
+    }
+  }
+
+  /* register pipeline of descriptors and row bounds */
+  int4 d_cur = make_int4(0, 0, 0, 0), d_nxt = make_int4(0, 0, 0, 0);
+  if (t < ntiles) d_cur = __ldg(&tiles[t]);
+  if (t + stride < ntiles) d_nxt = __ldg(&tiles[t + stride]);
+  int b_cur = 0, e_cur = 0, row_cur = -1;
+  double y_cur = 0.0;
+  auto load_row = [&](const int4 &d, int &b, int &e, int &row, double &y0) {
+    row = -1; b = e = 0;
+    if (r < d.y - d.x) {
+      const int p = d.x + r;
+      b = __ldg(&ci[p]); e = __ldg(&ci[p + 1]);
+      row = rindex ? __ldg(&rindex[p]) : p;
+      if (ADD && g == 0) y0 = yin[row];
+    }
+  };
+  if (t < ntiles) load_row(d_cur, b_cur, e_cur, row_cur, y_cur);
+
+  double dot = 0.0;
+  for (int it = 0; t < ntiles; it++, t += stride) {
+    const int s = it % STAGES;
+    const uint32_t parity = (uint32_t)((it / STAGES) & 1);
+    /* prefetch: bounds of the next tile, descriptor of the one after */
+    int b_nxt = 0, e_nxt = 0, row_nxt = -1;
+    double y_nxt = 0.0;
+    int4 d_nn = make_int4(0, 0, 0, 0);
+    if (t + stride < ntiles) load_row(d_nxt, b_nxt, e_nxt, row_nxt, y_nxt);
+    if (t + 2 * stride < ntiles) d_nn = __ldg(&tiles[t + 2 * stride]);
+
+    b200_mbar_wait(&bars[s], parity);
+    {
+      const int ka = d_cur.z & ~3;
+      double    *sa = s_a + (size_t)s * SE - ka;             /* indexed by the global entry number */
+      const int *sj = s_j + (size_t)s * SE - ka;
+      if (d_cur.y < 0) {
+        /* one chunk of a long row: every lane strides the chunk, fixed-shape block tree, partial -> longpart[slot] */
+        double p0 = 0.0, p1 = 0.0;
+        int k = d_cur.z + tid;
+        for (; k + THREADS < d_cur.w; k += 2 * THREADS) {
+          p0 += sa[k] * __ldg(&x[sj[k]]);
+          p1 += sa[k + THREADS] * __ldg(&x[sj[k + THREADS]]);
+        }
+        if (k < d_cur.w) p0 += sa[k] * __ldg(&x[sj[k]]);
+        double v = p0 + p1;
+        const int lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_red[wid] = v;
+        __syncthreads();
+        if (tid == 0) {
+          double w = 0.0;
+#pragma unroll
+          for (int q = 0; q < THREADS / 32; q++) w += s_red[q];
+          longpart[-d_cur.y - 1] = w;
+        }
+      } else {
+        if (PARK) {
+          /* balanced gather pass: products parked in place of the values, then the row sums read shared memory only */
+#pragma unroll 8
+          for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldg(&x[sj[k]]);
+          __syncthreads();
+        }
+        if (G == 1) {
+          if (row_cur >= 0) {
+            double sum = ADD ? y_cur : 0.0;
+            if (PARK) {
+#pragma unroll 4
+              for (int k = b_cur; k < e_cur; k++) sum += sa[k];
+            } else {
+#pragma unroll 4
+              for (int k = b_cur; k < e_cur; k++) sum += sa[k] * __ldg(&x[sj[k]]);
+            }
+            z[row_cur] = sum;
+            if (DOT) dot += __ldg(&x[row_cur]) * sum;
+          }
+        } else {
+          /* lanes without a row have b == e == 0 and fall through to the (warp-converged) shuffles */
+          double sum = 0.0;
+          if (PARK) {
+#pragma unroll 4
+            for (int k = b_cur + g; k < e_cur; k += G) sum += sa[k];
+          } else {
+#pragma unroll 4
+            for (int k = b_cur + g; k < e_cur; k += G) sum += sa[k] * __ldg(&x[sj[k]]);
+          }
+          __syncwarp();
+#pragma unroll
+          for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
+          if (g == 0 && row_cur >= 0) {
+            if (ADD) sum = y_cur + sum;
+            z[row_cur] = sum;
+            if (DOT) dot += __ldg(&x[row_cur]) * sum;
+          }
+        }
+      }
+    }
+    __syncthreads();                                          /* everyone is done with stage s */
+    if (tid == 0) {
+      const int tt = t + STAGES * stride;
+      if (tt < ntiles) issue(s, __ldg(&tiles[tt]));
+    }
+    d_cur = d_nxt; d_nxt = d_nn;
+    b_cur = b_nxt; e_cur = e_nxt; row_cur = row_nxt; y_cur = y_nxt;
+  }
+
+  if (DOT) {
+    const int lane = tid & 31, wid = tid >> 5;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+    if (lane == 0) s_red[wid] = dot;
+    __syncthreads();
+    if (wid == 0) {
+      double v = (lane < THREADS / 32) ? s_red[lane] : 0.0;
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) dotpart[blockIdx.x] = v;
+    }
+  }
+}
+
+/* long rows: sum the chunk partials of each row in chunk order (fixed association), add y, write z (+ the x.z term) */
+template <bool ADD, bool DOT>
+__global__ void __launch_bounds__(128)
+spmv_long_finish_kernel(int nlong, const int *__restrict__ longrows, const int *__restrict__ longstart,
+                        const int *__restrict__ rindex, const double *__restrict__ longpart,
+                        const double *__restrict__ x, const double *yin, double *z, double *__restrict__ dotpart)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= nlong) return;
+  const int r = __ldg(&longrows[i]);
+  const int row = rindex ? __ldg(&rindex[r]) : r;
+  double v = 0.0;
+  for (int c = __ldg(&longstart[i]); c < __ldg(&longstart[i + 1]); c++) v += longpart[c];
+  const double out = ADD ? yin[row] + v : v;
+  z[row] = out;
+  if (DOT) dotpart[i] = __ldg(&x[row]) * out;
+}
+
+#endif /* B200_SPMV_KERNELS_CUH */

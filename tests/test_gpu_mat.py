@@ -1,6 +1,7 @@
 """AIJ MatMult / MatMultAdd / MatGetDiagonal on the B200 against the reference's MatMult_SeqAIJ (oracle/_ref).
-Rows that go through the stream tiles are summed left to right like aij.h:384 -> BIT-EXACT; long rows (> 256
-entries) use a tree -> |dy_i| <= 1e-12 * sum_j |a_ij x_j| (the tolerance BASELINE.json states)."""
+Tile rows handled by ONE lane (lanes_per_row == 1: the automatic choice for short rows such as the 5/7-point stencils,
+or forced with spmv_tuning) are summed left to right like aij.h:384 -> BIT-EXACT; rows shared by several lanes and long
+rows use a fixed tree -> |dy_i| <= 1e-12 * sum_j |a_ij x_j| (the tolerance BASELINE.json states)."""
 import numpy as np
 import pytest
 
@@ -9,8 +10,16 @@ from conftest import ex5_matrix
 pytestmark = pytest.mark.gpu
 
 
-def _check(gpu, R, P, m, n, ip, j, a, seed=2, exact=True):
-    A = gpu.Mat.from_csr(m, n, ip, j, a)
+def _check(gpu, R, P, m, n, ip, j, a, seed=2, exact=True, lanes=-1, park=-1, long_thresh=-1):
+    gpu.spmv_tuning(lanes_per_row=lanes, park=park, long_thresh=long_thresh)
+    try:
+        A = gpu.Mat.from_csr(m, n, ip, j, a)
+    finally:
+        gpu.spmv_tuning()
+    info = A.bin_info()
+    if lanes > 0:
+        assert info["lanes_per_row"] == lanes
+    exact = exact and info["lanes_per_row"] == 1 and info["nlong"] == 0
     ref = R.RefMat(m, n, ip, j, a, no_inode=True)
     xh, yh = P.random_vector(n, seed), P.random_vector(m, seed + 1)
     x, y, z = gpu.Vec(n, xh), gpu.Vec(m, yh), gpu.Vec(m)
@@ -74,7 +83,17 @@ def test_structured_bit_exact(gpu, R, P, case):
         ip, j, a, m, n = np.array([0]), np.zeros(0, np.int32), np.zeros(0), 0, 5
     elif case == "all_empty":
         ip, j, a, m, n = np.zeros(11, np.int64), np.zeros(0, np.int32), np.zeros(0), 10, 10
-    _check(gpu, R, P, m, n, np.asarray(ip, np.int64), np.asarray(j, np.int32), a)
+    ip, j = np.asarray(ip, np.int64), np.asarray(j, np.int32)
+    A = _check(gpu, R, P, m, n, ip, j, a)                       # automatic lanes per row (tolerance when > 1)
+    if case in ("lap2d_ex2", "lap7", "rect", "empty_rows"):
+        assert A.bin_info()["lanes_per_row"] == 1               # short rows: reference order by default
+    _check(gpu, R, P, m, n, ip, j, a, lanes=1)                  # one lane per row: bit-exact for every pattern
+    _check(gpu, R, P, m, n, ip, j, a, lanes=1, park=1)          # ... also when the products are parked first
+    for lanes in (2, 8, 32):
+        _check(gpu, R, P, m, n, ip, j, a, lanes=lanes, park=lanes == 8)
+    if len(a) > 64:                                             # every row becomes a chain of chunk tiles
+        B = _check(gpu, R, P, m, n, ip, j, a, long_thresh=2)
+        assert B.bin_info()["nlong"] > 0
 
 
 def test_compressed_rows_offdiag_like(gpu, R, P):
@@ -97,13 +116,15 @@ def test_irregular_powerlaw(gpu, R, P):
     assert np.diff(ip).max() > 1000
     A = _check(gpu, R, P, N, N, ip, j, a, exact=False)
     info = A.bin_info()
-    assert info["nlong"] > 0 and info["ntiles"] > 0
-    # rows at or below the threshold are still bit-exact
+    assert info["nlong"] > 0 and info["ntiles"] > 0 and info["park"]
+    _check(gpu, R, P, N, N, ip, j, a, exact=False, park=0)
+    # with one lane per row, rows at or below the long-row threshold are still bit-exact
+    A = _check(gpu, R, P, N, N, ip, j, a, exact=False, lanes=1)
     ref = R.RefMat(N, N, ip, j, a)
     xh = P.random_vector(N, 2)
     x, y = gpu.Vec(N, xh), gpu.Vec(N)
     A.mult(x, y)
-    short = np.diff(ip) <= 256
+    short = np.diff(ip) <= A.bin_info()["long_thresh"]
     assert np.array_equal(y.get_array()[short], ref.mult(xh)[short])
 
 
