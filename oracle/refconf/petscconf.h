@@ -76,6 +76,13 @@
 #define PETSC_HAVE_DLOPEN 1
 #define PETSC_HAVE_DLSYM 1
 #define PETSC_HAVE_DLERROR 1
+/* -dll_prepend / -dll_append really dlopen() the named library (src/sys/dll/dlimpl.c:9,255): this is how the
+   out-of-tree B200 plugin gets into an unmodified example program */
+#define PETSC_HAVE_DYNAMIC_LIBRARIES 1
+#define PETSC_HAVE_RTLD_LAZY 1
+#define PETSC_HAVE_RTLD_NOW 1
+#define PETSC_HAVE_RTLD_GLOBAL 1
+#define PETSC_HAVE_RTLD_LOCAL 1
 #define PETSC_HAVE_DLCLOSE 1
 #define PETSC_HAVE_ISNAN 1
 #define PETSC_HAVE_ISINF 1

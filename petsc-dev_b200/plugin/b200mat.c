@@ -1,0 +1,354 @@
+/* b200mat.c — MATSEQAIJB200 / MATMPIAIJB200 / "aijb200": AIJ matrices whose MatMult / MatMultAdd run on a B200.
+ *
+ * Mirrors MatCreate_SeqAIJCUSP (reference src/mat/impls/aij/seq/seqcusp/aijcusp.cu:657-681) and MatCreate_MPIAIJCUSP
+ * (src/mat/impls/aij/mpi/mpicusp/mpiaijcusp.cu:192-226): inherit the complete host CSR type (MatCreate_SeqAIJ aij.c:3886,
+ * MatCreate_MPIAIJ mpiaij.c:5617 — preallocation, MatSetValues, assembly, views, MatGetDiagonal ... all stay host code),
+ * override mult / multadd / getvecs / destroy, switch the inode path off (aijcusp.cu:665).
+ *
+ * Device copy: built lazily at the first MatMult after the matrix changed.  "Changed" is detected with the object state
+ * every mutating Mat front end bumps (MatAssemblyEnd, MatScale, MatShift, MatZeroEntries, MatDiagonalScale, MatZeroRows:
+ * PetscObjectStateIncrease in src/mat/interface/matrix.c) — the PETSC_HAVE_CUSP build marks the same places with
+ * valid_GPU_matrix = PETSC_CUSP_CPU (matrix.c:1085-1089,4917-4921).  When the row offsets are unchanged only the values
+ * are re-sent (b200_mat_update_values), not the whole matrix as MatCUSPCopyToGPU does (aijcusp.cu:138-152). */
+#include "petscb200plugin.h"
+#include <../src/mat/impls/aij/seq/aij.h>
+#include <../src/mat/impls/aij/mpi/mpiaij.h>
+#include <petsc-private/vecimpl.h>
+#include "petscb200.h"
+
+extern PetscInt PetscB200MatUploads, PetscB200MatValueUpdates;
+
+#define CHKB200(call) do { int b200rc_ = (call); if (b200rc_) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_LIB,"libpetscb200 error %d: %s",b200rc_,b200_last_error()); } while (0)
+
+typedef struct {
+  b200_mat  mat;          /* device CSR + row binning                           */
+  PetscInt  state;        /* object state of the host matrix at the last upload */
+  PetscInt  m,nz;
+  PetscInt *i;            /* host copy of the uploaded row offsets              */
+} Mat_SeqAIJB200;
+
+typedef struct {
+  b200_mat  mat;          /* diagonal block, off-diagonal block, ghost plan     */
+  PetscInt  state,stateA,stateB;
+} Mat_MPIAIJB200;
+
+/* ------------------------------------------------------------------------------------------------ sequential */
+#undef __FUNCT__
+#define __FUNCT__ "MatB200CopyToDevice_SeqAIJ"
+static PetscErrorCode MatB200CopyToDevice_SeqAIJ(Mat A)                           /* MatCUSPCopyToGPU aijcusp.cu:126 */
+{
+  Mat_SeqAIJ     *a = (Mat_SeqAIJ*)A->data;
+  Mat_SeqAIJB200 *d = (Mat_SeqAIJB200*)A->spptr;
+  PetscInt       m = A->rmap->n;
+  PetscBool      same = PETSC_FALSE;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (!A->assembled) SETERRQ(((PetscObject)A)->comm,PETSC_ERR_ARG_WRONGSTATE,"Not for unassembled matrix");
+  if (d->mat && d->state == ((PetscObject)A)->state) PetscFunctionReturn(0);
+  if (d->mat && d->m == m && d->nz == a->nz) {
+    ierr = PetscMemcmp(d->i,a->i,(m+1)*sizeof(PetscInt),&same);CHKERRQ(ierr);
+  }
+  if (same) {
+    CHKB200(b200_mat_update_values(d->mat,a->a));
+    PetscB200MatValueUpdates++;
+  } else {
+    if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }
+    ierr = PetscFree(d->i);CHKERRQ(ierr);
+    CHKB200(b200_mat_create_seqaij(m,A->cmap->n,a->i,a->j,a->a,&d->mat));
+    ierr = PetscMalloc((m+1)*sizeof(PetscInt),&d->i);CHKERRQ(ierr);
+    ierr = PetscMemcpy(d->i,a->i,(m+1)*sizeof(PetscInt));CHKERRQ(ierr);
+    d->m = m; d->nz = a->nz;
+    PetscB200MatUploads++;
+  }
+  d->state = ((PetscObject)A)->state;
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMult_SeqAIJB200"
+static PetscErrorCode MatMult_SeqAIJB200(Mat A,Vec xx,Vec yy)                     /* MatMult_SeqAIJ aij.c:1225 */
+{
+  const PetscScalar *x;
+  PetscScalar       *y;
+  double            flops;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_SeqAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceWrite(yy,&y);CHKERRQ(ierr);
+  CHKB200(b200_mat_mult(((Mat_SeqAIJB200*)A->spptr)->mat,x,y));
+  CHKB200(b200_mat_flops(((Mat_SeqAIJB200*)A->spptr)->mat,&flops));               /* 2 nz - nonzerorow, aij.c:1281 */
+  ierr = PetscLogFlops(flops);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMultAdd_SeqAIJB200"
+static PetscErrorCode MatMultAdd_SeqAIJB200(Mat A,Vec xx,Vec yy,Vec zz)           /* MatMultAdd_SeqAIJ aij.c:1291 */
+{
+  Mat_SeqAIJ        *a = (Mat_SeqAIJ*)A->data;
+  const PetscScalar *x,*y;
+  PetscScalar       *z;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_SeqAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  if (zz == yy) { ierr = VecB200GetDeviceReadWrite(zz,&z);CHKERRQ(ierr); y = z; }
+  else {
+    ierr = VecB200GetDeviceRead(yy,&y);CHKERRQ(ierr);
+    ierr = VecB200GetDeviceWrite(zz,&z);CHKERRQ(ierr);
+  }
+  CHKB200(b200_mat_multadd(((Mat_SeqAIJB200*)A->spptr)->mat,x,y,z));
+  ierr = PetscLogFlops(2.0*a->nz);CHKERRQ(ierr);                                  /* aij.c:1343 */
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatGetVecs_SeqAIJB200"
+static PetscErrorCode MatGetVecs_SeqAIJB200(Mat mat,Vec *right,Vec *left)         /* MatGetVecs_SeqAIJCUSP aijcusp.cu:324 */
+{
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (right) {
+    ierr = VecCreate(((PetscObject)mat)->comm,right);CHKERRQ(ierr);
+    ierr = VecSetSizes(*right,mat->cmap->n,PETSC_DETERMINE);CHKERRQ(ierr);
+    ierr = VecSetBlockSize(*right,mat->rmap->bs);CHKERRQ(ierr);
+    ierr = VecSetType(*right,VECSEQB200);CHKERRQ(ierr);
+    ierr = PetscLayoutReference(mat->cmap,&(*right)->map);CHKERRQ(ierr);
+  }
+  if (left) {
+    ierr = VecCreate(((PetscObject)mat)->comm,left);CHKERRQ(ierr);
+    ierr = VecSetSizes(*left,mat->rmap->n,PETSC_DETERMINE);CHKERRQ(ierr);
+    ierr = VecSetBlockSize(*left,mat->rmap->bs);CHKERRQ(ierr);
+    ierr = VecSetType(*left,VECSEQB200);CHKERRQ(ierr);
+    ierr = PetscLayoutReference(mat->rmap,&(*left)->map);CHKERRQ(ierr);
+  }
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatDestroy_SeqAIJB200"
+static PetscErrorCode MatDestroy_SeqAIJB200(Mat A)                                /* MatDestroy_SeqAIJCUSP aijcusp.cu:566 */
+{
+  Mat_SeqAIJB200 *d = (Mat_SeqAIJB200*)A->spptr;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (d) {
+    if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); }
+    ierr = PetscFree(d->i);CHKERRQ(ierr);
+    ierr = PetscFree(d);CHKERRQ(ierr);
+  }
+  A->spptr = 0;                                                                   /* MatDestroy frees a non-null spptr */
+  ierr = MatDestroy_SeqAIJ(A);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+EXTERN_C_BEGIN
+#undef __FUNCT__
+#define __FUNCT__ "MatCreate_SeqAIJB200"
+PetscErrorCode MatCreate_SeqAIJB200(Mat B)
+{
+  Mat_SeqAIJB200 *d;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = MatCreate_SeqAIJ(B);CHKERRQ(ierr);
+  ((Mat_SeqAIJ*)B->data)->inode.use = PETSC_FALSE;                                /* aijcusp.cu:665 */
+  ierr = PetscNewLog(B,Mat_SeqAIJB200,&d);CHKERRQ(ierr);
+  B->spptr        = (void*)d;
+  B->ops->mult    = MatMult_SeqAIJB200;
+  B->ops->multadd = MatMultAdd_SeqAIJB200;
+  B->ops->getvecs = MatGetVecs_SeqAIJB200;
+  B->ops->destroy = MatDestroy_SeqAIJB200;
+  ierr = PetscObjectChangeTypeName((PetscObject)B,MATSEQAIJB200);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+EXTERN_C_END
+
+/* ------------------------------------------------------------------------------------------------ parallel */
+#undef __FUNCT__
+#define __FUNCT__ "MatMPIAIJSetPreallocation_MPIAIJB200"
+static PetscErrorCode MatMPIAIJSetPreallocation_MPIAIJB200(Mat B,PetscInt d_nz,const PetscInt d_nnz[],PetscInt o_nz,const PetscInt o_nnz[])
+{                                                                                 /* mpiaijcusp.cu:9-55 */
+  Mat_MPIAIJ     *b = (Mat_MPIAIJ*)B->data;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (!B->preallocated) {
+    /* the two sequential blocks are of our type, so every host op on them stays coherent with the device copy */
+    ierr = PetscLayoutSetUp(B->rmap);CHKERRQ(ierr);
+    ierr = PetscLayoutSetUp(B->cmap);CHKERRQ(ierr);
+    ierr = MatCreate(PETSC_COMM_SELF,&b->A);CHKERRQ(ierr);
+    ierr = MatSetSizes(b->A,B->rmap->n,B->cmap->n,B->rmap->n,B->cmap->n);CHKERRQ(ierr);
+    ierr = MatSetBlockSizes(b->A,B->rmap->bs,B->cmap->bs);CHKERRQ(ierr);
+    ierr = MatSetType(b->A,MATSEQAIJB200);CHKERRQ(ierr);
+    ierr = PetscLogObjectParent(B,b->A);CHKERRQ(ierr);
+    ierr = MatCreate(PETSC_COMM_SELF,&b->B);CHKERRQ(ierr);
+    ierr = MatSetSizes(b->B,B->rmap->n,B->cmap->N,B->rmap->n,B->cmap->N);CHKERRQ(ierr);
+    ierr = MatSetBlockSizes(b->B,B->rmap->bs,B->cmap->bs);CHKERRQ(ierr);
+    ierr = MatSetType(b->B,MATSEQAIJB200);CHKERRQ(ierr);
+    ierr = PetscLogObjectParent(B,b->B);CHKERRQ(ierr);
+    B->preallocated = PETSC_TRUE;                                                 /* the base routine then only preallocates */
+  }
+  ierr = MatMPIAIJSetPreallocation_MPIAIJ(B,d_nz,d_nnz,o_nz,o_nnz);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+/* (re)build the device operator from the assembled host pieces: Mat_MPIAIJ::A, ::B (columns already compacted to
+ * ghost ids by MatSetUpMultiply_MPIAIJ mmaij.c:56-63), ::garray, and the VecScatter_MPI_General send/receive lists of
+ * ::Mvctx (vpscat.c:1827-1879) — what VecScatterInitializeForGPU digs out for the CUSP path (vscatcusp.c:29-133). */
+#undef __FUNCT__
+#define __FUNCT__ "MatB200CopyToDevice_MPIAIJ"
+static PetscErrorCode MatB200CopyToDevice_MPIAIJ(Mat A)
+{
+  Mat_MPIAIJ     *a  = (Mat_MPIAIJ*)A->data;
+  Mat_MPIAIJB200 *d  = (Mat_MPIAIJB200*)a->spptr;
+  Mat_SeqAIJ     *ad = (Mat_SeqAIJ*)a->A->data,*ao = (Mat_SeqAIJ*)a->B->data;
+  PetscInt       nghost = a->B->cmap->n,nto = 0,nfrom = 0,i,k,c;
+  int            *to_procs = 0,*to_starts = 0,*to_indices = 0,*from_procs = 0,*from_starts = 0;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (!A->assembled) SETERRQ(((PetscObject)A)->comm,PETSC_ERR_ARG_WRONGSTATE,"Not for unassembled matrix");
+  if (d->mat && d->state == ((PetscObject)A)->state && d->stateA == ((PetscObject)a->A)->state && d->stateB == ((PetscObject)a->B)->state) PetscFunctionReturn(0);
+  if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }
+  if (a->size > 1) {
+    VecScatter_MPI_General *to = (VecScatter_MPI_General*)a->Mvctx->todata,*from = (VecScatter_MPI_General*)a->Mvctx->fromdata;
+    PetscInt               bs = to->bs;
+    if (to->type != VEC_SCATTER_MPI_GENERAL || from->type != VEC_SCATTER_MPI_GENERAL) SETERRQ(((PetscObject)A)->comm,PETSC_ERR_SUP,"MatMult scatter is not the general parallel scatter");
+    nto = to->n; nfrom = from->n;
+    ierr = PetscMalloc5(nto+1,int,&to_procs,nto+1,int,&to_starts,bs*to->starts[nto]+1,int,&to_indices,nfrom+1,int,&from_procs,nfrom+1,int,&from_starts);CHKERRQ(ierr);
+    for (i=0; i<nto; i++)    to_procs[i] = to->procs[i];
+    for (i=0; i<=nto; i++)   to_starts[i] = bs*to->starts[i];
+    for (k=0; k<to->starts[nto]; k++) for (c=0; c<bs; c++) to_indices[bs*k+c] = to->indices[k]+c;   /* Pack_bs, vpscat.c:674 */
+    for (i=0; i<nfrom; i++)  from_procs[i] = from->procs[i];
+    for (i=0; i<=nfrom; i++) from_starts[i] = bs*from->starts[i];
+    /* receives land in lvec in order: MatSetUpMultiply's `to` index set is the stride 0..nghost-1 (mmaij.c:144) */
+    for (k=0; k<from->starts[nfrom]; k++) if (from->indices[k] != bs*k) SETERRQ(((PetscObject)A)->comm,PETSC_ERR_PLIB,"Ghost receive positions are not contiguous");
+  }
+  CHKB200(b200_mat_create_mpiaij(A->rmap->n,A->cmap->n,A->cmap->N,ad->i,ad->j,ad->a,nghost,ao->i,ao->j,ao->a,a->garray,
+                                 nto,to_procs,to_starts,to_indices,nfrom,from_procs,from_starts,&d->mat));
+  if (a->size > 1) { ierr = PetscFree5(to_procs,to_starts,to_indices,from_procs,from_starts);CHKERRQ(ierr); }
+  PetscB200MatUploads++;
+  d->state = ((PetscObject)A)->state; d->stateA = ((PetscObject)a->A)->state; d->stateB = ((PetscObject)a->B)->state;
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMult_MPIAIJB200"
+static PetscErrorCode MatMult_MPIAIJB200(Mat A,Vec xx,Vec yy)                     /* MatMult_MPIAIJ mpiaij.c:1102 */
+{
+  Mat_MPIAIJ        *a = (Mat_MPIAIJ*)A->data;
+  const PetscScalar *x;
+  PetscScalar       *y;
+  double            flops;
+  PetscInt          nt;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = VecGetLocalSize(xx,&nt);CHKERRQ(ierr);
+  if (nt != A->cmap->n) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_ARG_SIZ,"Incompatible partition of A (%D) and xx (%D)",A->cmap->n,nt);
+  ierr = MatB200CopyToDevice_MPIAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceWrite(yy,&y);CHKERRQ(ierr);
+  /* ghost exchange (GPU to GPU) overlapped with the diagonal block, then y += B lvec: all inside the library */
+  CHKB200(b200_mat_mult(((Mat_MPIAIJB200*)a->spptr)->mat,x,y));
+  CHKB200(b200_mat_flops(((Mat_MPIAIJB200*)a->spptr)->mat,&flops));
+  ierr = PetscLogFlops(flops);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMultAdd_MPIAIJB200"
+static PetscErrorCode MatMultAdd_MPIAIJB200(Mat A,Vec xx,Vec yy,Vec zz)           /* MatMultAdd_MPIAIJ mpiaij.c:1132 */
+{
+  Mat_MPIAIJ        *a = (Mat_MPIAIJ*)A->data;
+  const PetscScalar *x,*y;
+  PetscScalar       *z;
+  double            flops;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_MPIAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  if (zz == yy) { ierr = VecB200GetDeviceReadWrite(zz,&z);CHKERRQ(ierr); y = z; }
+  else {
+    ierr = VecB200GetDeviceRead(yy,&y);CHKERRQ(ierr);
+    ierr = VecB200GetDeviceWrite(zz,&z);CHKERRQ(ierr);
+  }
+  CHKB200(b200_mat_multadd(((Mat_MPIAIJB200*)a->spptr)->mat,x,y,z));
+  CHKB200(b200_mat_flops(((Mat_MPIAIJB200*)a->spptr)->mat,&flops));
+  ierr = PetscLogFlops(flops + A->rmap->n);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatGetVecs_MPIAIJB200"
+static PetscErrorCode MatGetVecs_MPIAIJB200(Mat mat,Vec *right,Vec *left)         /* MatGetVecs_MPIAIJCUSP mpiaijcusp.cu:59 */
+{
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (right) {
+    ierr = VecCreate(((PetscObject)mat)->comm,right);CHKERRQ(ierr);
+    ierr = VecSetSizes(*right,mat->cmap->n,PETSC_DETERMINE);CHKERRQ(ierr);
+    ierr = VecSetBlockSize(*right,mat->rmap->bs);CHKERRQ(ierr);
+    ierr = VecSetType(*right,VECMPIB200);CHKERRQ(ierr);
+    ierr = PetscLayoutReference(mat->cmap,&(*right)->map);CHKERRQ(ierr);
+  }
+  if (left) {
+    ierr = VecCreate(((PetscObject)mat)->comm,left);CHKERRQ(ierr);
+    ierr = VecSetSizes(*left,mat->rmap->n,PETSC_DETERMINE);CHKERRQ(ierr);
+    ierr = VecSetBlockSize(*left,mat->rmap->bs);CHKERRQ(ierr);
+    ierr = VecSetType(*left,VECMPIB200);CHKERRQ(ierr);
+    ierr = PetscLayoutReference(mat->rmap,&(*left)->map);CHKERRQ(ierr);
+  }
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatDestroy_MPIAIJB200"
+static PetscErrorCode MatDestroy_MPIAIJB200(Mat A)                                /* MatDestroy_MPIAIJCUSP mpiaijcusp.cu:176 */
+{
+  Mat_MPIAIJ     *a = (Mat_MPIAIJ*)A->data;
+  Mat_MPIAIJB200 *d = (Mat_MPIAIJB200*)a->spptr;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (d) {
+    if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); }
+    ierr = PetscFree(d);CHKERRQ(ierr);
+    a->spptr = 0;
+  }
+  ierr = MatDestroy_MPIAIJ(A);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+EXTERN_C_BEGIN
+#undef __FUNCT__
+#define __FUNCT__ "MatCreate_MPIAIJB200"
+PetscErrorCode MatCreate_MPIAIJB200(Mat A)
+{
+  Mat_MPIAIJ     *a;
+  Mat_MPIAIJB200 *d;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = MatCreate_MPIAIJ(A);CHKERRQ(ierr);
+  ierr = PetscObjectComposeFunctionDynamic((PetscObject)A,"MatMPIAIJSetPreallocation_C","MatMPIAIJSetPreallocation_MPIAIJB200",MatMPIAIJSetPreallocation_MPIAIJB200);CHKERRQ(ierr);
+  a = (Mat_MPIAIJ*)A->data;
+  ierr = PetscNewLog(A,Mat_MPIAIJB200,&d);CHKERRQ(ierr);
+  a->spptr        = (void*)d;
+  A->ops->mult    = MatMult_MPIAIJB200;
+  A->ops->multadd = MatMultAdd_MPIAIJB200;
+  A->ops->getvecs = MatGetVecs_MPIAIJB200;
+  A->ops->destroy = MatDestroy_MPIAIJB200;
+  ierr = PetscObjectChangeTypeName((PetscObject)A,MATMPIAIJB200);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+EXTERN_C_END

@@ -1,0 +1,62 @@
+/* b200reg.c — registration of the B200 Vec/Mat types with a running PETSc.
+ *
+ * What MatRegisterAll / VecRegisterAll do for the CUSP types inside the library (reference
+ * src/mat/interface/matregis.c:134-137, src/vec/vec/interface/vecregall.c:46-49) an out-of-tree plugin does after
+ * PetscInitialize with the same public calls (include/petscmat.h:183-227, include/petscvec.h:319-364). */
+#include "petscb200plugin.h"
+#include "petscb200.h"
+
+static PetscBool PetscB200Registered = PETSC_FALSE;
+
+#undef __FUNCT__
+#define __FUNCT__ "PetscB200Finalize"
+static PetscErrorCode PetscB200Finalize(void)
+{
+  PetscFunctionBegin;
+  PetscB200Registered = PETSC_FALSE;
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "PetscB200Register"
+PetscErrorCode PetscB200Register(void)
+{
+  PetscInt       device = -1;
+  PetscMPIInt    rank;
+  int            ndev = 0;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (PetscB200Registered) PetscFunctionReturn(0);
+  /* one process per GPU: rank r drives device r mod (devices on the node) unless -b200_device says otherwise
+     (the reference never picks a device, src/sys/objects/pinit.c:838-846) */
+  ierr = MPI_Comm_rank(PETSC_COMM_WORLD,&rank);CHKERRQ(ierr);
+  ierr = PetscOptionsGetInt(PETSC_NULL,"-b200_device",&device,PETSC_NULL);CHKERRQ(ierr);
+  if (device < 0) {
+    if (b200_device_count(&ndev) || ndev < 1) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"No usable CUDA device for the B200 types: %s",b200_last_error());
+    device = rank % ndev;
+  }
+  if (b200_init((int)device)) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_init(%D) failed: %s",device,b200_last_error());
+  ierr = VecRegister(VECSEQB200,0,"VecCreate_SeqB200",VecCreate_SeqB200);CHKERRQ(ierr);
+  ierr = VecRegister(VECMPIB200,0,"VecCreate_MPIB200",VecCreate_MPIB200);CHKERRQ(ierr);
+  ierr = VecRegister(VECB200,   0,"VecCreate_B200",   VecCreate_B200);CHKERRQ(ierr);
+  ierr = MatRegisterBaseName(MATAIJB200,MATSEQAIJB200,MATMPIAIJB200);CHKERRQ(ierr);
+  ierr = MatRegister(MATSEQAIJB200,0,"MatCreate_SeqAIJB200",MatCreate_SeqAIJB200);CHKERRQ(ierr);
+  ierr = MatRegister(MATMPIAIJB200,0,"MatCreate_MPIAIJB200",MatCreate_MPIAIJB200);CHKERRQ(ierr);
+  ierr = PetscRegisterFinalize(PetscB200Finalize);CHKERRQ(ierr);
+  PetscB200Registered = PETSC_TRUE;
+  PetscFunctionReturn(0);
+}
+
+/* run by PetscDLLibraryPrepend/Append when the program is started with -dll_prepend <this library>
+   (src/sys/dll/dl.c:185-190 looks the symbol up by the library's base name) */
+#undef __FUNCT__
+#define __FUNCT__ "PetscDLLibraryRegister_petscb200plugin"
+PetscErrorCode PetscDLLibraryRegister_petscb200plugin(const char path[])
+{
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = PetscB200Register();CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
