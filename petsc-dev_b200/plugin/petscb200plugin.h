@@ -27,7 +27,6 @@
 #define MATMPIAIJB200 "mpiaijb200"
 #define MATAIJB200    "aijb200"
 
-PETSC_EXTERN_CXX_BEGIN
 EXTERN_C_BEGIN
 extern PetscErrorCode PetscB200Register(void);
 extern PetscErrorCode PetscDLLibraryRegister_petscb200plugin(const char path[]);
@@ -48,6 +47,5 @@ extern PetscErrorCode VecB200GetDeviceReadWrite(Vec, PetscScalar **);
 extern PetscErrorCode VecB200GetWhere(Vec, B200VecWhere *);
 /* counters for tests: host<->device copies the coherence protocol performed, device matrix uploads */
 extern PetscErrorCode PetscB200GetCounters(PetscInt *h2d, PetscInt *d2h, PetscInt *matuploads, PetscInt *matvalueupdates);
-PETSC_EXTERN_CXX_END
 
 #endif

@@ -1,0 +1,42 @@
+"""The reference's own example programs (compiled UNMODIFIED into oracle/_ref/bin by petsc-dev_b200/plugin/build_plugin.py)
+and the option sets the reference's makefiles run them with (file:line of each `runex*` target), used three ways:
+  reference arm : <prog> args + ref_args            -> the reference's CPU Mat/Vec types
+  golden        : the reference's committed output file, where one exists
+  B200 arm      : <prog> args + -dll_prepend libpetscb200plugin.so + b200_args -> the new types, nothing else changed
+"""
+import os
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "oracle", "_ref", "bin")
+PLUGIN = os.path.join(ROOT, "petsc-dev_b200", "lib", "libpetscb200plugin.so")
+B200 = ["-mat_type", "aijb200", "-vec_type", "b200"]
+
+CASES = {
+    # src/ksp/ksp/examples/tutorials/makefile:317 (GMRES + ILU(0): the factorisation and MatSolve stay host code and
+    # reach the device vectors through VecGetArray -> exercises the coherence seam)
+    "ksp_ex2_1": dict(prog="ksp_ex2", args=["-ksp_monitor_short", "-m", "5", "-n", "5", "-ksp_gmres_cgs_refinement_type", "refine_always"],
+                      b200_args=B200, golden="src/ksp/ksp/examples/tutorials/output/ex2_1.out"),
+    # BASELINE.json configs[0] at a size the CPU finishes at once: ex2 with KSPCG + PCJACOBI
+    "ksp_ex2_cg_jacobi": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "40", "-n", "37", "-ksp_type", "cg", "-pc_type", "jacobi"],
+                              b200_args=B200, history=True),
+    "ksp_ex2_gmres_jacobi": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "33", "-n", "41", "-ksp_type", "gmres", "-pc_type", "jacobi", "-ksp_gmres_restart", "30"],
+                                 b200_args=B200, history=True),
+    "ksp_ex2_cg_random": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "25", "-n", "25", "-ksp_type", "cg", "-pc_type", "jacobi", "-random_exact_sol"],
+                              b200_args=B200, history=True),
+    "ksp_ex2_mpiaij": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "30", "-n", "30", "-ksp_type", "cg", "-pc_type", "jacobi"],
+                           ref_args=["-mat_type", "mpiaij", "-vec_type", "mpi"], b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"], history=True),
+    # src/mat/examples/tests/makefile:753,774,795
+    "mat_ex5_11_A": dict(prog="mat_ex5", args=["-rectA"], ref_args=["-mat_type", "seqaij"], b200_args=["-mat_type", "seqaijb200", "-vec_type", "seqb200"],
+                         golden="src/mat/examples/tests/output/ex5_11_A.out"),
+    "mat_ex5_21": dict(prog="mat_ex5", args=[], ref_args=["-mat_type", "mpiaij"], b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"],
+                       golden="src/mat/examples/tests/output/ex5_21.out"),
+    "mat_ex5_31": dict(prog="mat_ex5", args=["-test_diagonalscale"], ref_args=["-mat_type", "mpiaij"], b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"],
+                       golden="src/mat/examples/tests/output/ex5_31.out"),
+    # src/vec/vec/examples/tutorials/makefile:142 (VecDot, VecMDot, VecScale, VecCopy, VecAXPY, VecAYPX, VecWAXPY,
+    # VecPointwiseMult/Divide, VecMAXPY, VecNorm)
+    "vec_tut_ex1": dict(prog="vec_tut_ex1", args=[], b200_args=["-vec_type", "b200"], golden="src/vec/vec/examples/tutorials/output/ex1_1.out"),
+    # src/vec/vec/examples/tests/makefile:418 (VecMDot against VecDot)
+    "vec_ex43": dict(prog="vec_ex43", args=[], b200_args=["-vec_type", "b200"], golden="src/vec/vec/examples/tests/output/ex43_1.out"),
+    # strided ops and VecMax/VecMin on one rank (golden files are for 2 ranks -> compared with the reference arm only)
+    "vec_ex21": dict(prog="vec_ex21", args=[], b200_args=["-vec_type", "b200"]),
+}
