@@ -138,6 +138,8 @@ def run_b200(args):
     else:
         import torch
         par.comm_init(rank, world, dist, device="cuda")
+        if args.transport == "p2p":
+            par.enable_p2p()
         ranges = par.split_ownership(Nglob, world)
         ai, aj, aa = P.laplace3d_7pt(nx, nx, nx * world, r0=int(ranges[rank]), r1=int(ranges[rank + 1]))
         host = par.setup_mpiaij_host(rank, world, ranges, ai - ai[0], aj, aa, Nglob, dist=dist, device="cuda")
@@ -237,10 +239,11 @@ def run_b200(args):
             "data": "synthetic",
             "config": {"workload": "configs[1]: 3D 7-point Laplacian %d^3 per GPU, AIJ MatMult (+KSPCG/Jacobi)" % nx,
                        "rows_per_gpu": m, "nnz_per_gpu": int(nz), "parallelism": "row slabs x%d (MPIAIJ diag+offdiag)" % world,
+                       "transport": "none (1 rank)" if world == 1 else ("NVLink peer stores, own kernels" if args.transport == "p2p" else "NCCL send/recv + allreduce"),
                        "l2_policy": "inputs (1.7 GB per GPU) larger than the 126 MB L2; no flush"},
             "gflops": (2.0 * nz * world - m * world) / (ms_step * 1e-3) / 1e9,
             "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "kernel": "spmv_stream_kernel<false,false>",
+                         "traffic": None, "kernel": "spmv_tile_kernel<G=1,PARK=0,ADD=0,DOT=0,256,2048,1>",
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "algorithmic_bytes_per_launch": B_alg},
             "kspcg": ksp,
@@ -275,6 +278,8 @@ def main():
     ap.add_argument("--nx", type=int, default=256)
     ap.add_argument("--cg-iters", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
+                    help="N > 1: ghost exchange + scalar allreduces over NVLink peer memory (own kernels) or NCCL")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -6,7 +6,17 @@
  * is Python, the system one otherwise) — grouped ncclSend/ncclRecv per neighbour straight into the ghost vector
  * (receives are contiguous because garray is sorted: `from->contiq`, vpscat.c:1951-1960), on a side stream that
  * overlaps the diagonal-block product.
- * Transport 2 (b200_comm_enable_p2p): NVLink peer stores — see the second half of this file.
+ * Transport 2 (b200_comm_enable_p2p): NVLink peer memory.  Every rank owns an "arena" (one cudaMalloc, exported with
+ * cudaIpcGetMemHandle, opened by every peer) holding its ghost vectors, arrival flags, credits and an allreduce inbox.
+ *   - ghost exchange = ONE kernel: gather x[indices] and store straight into the neighbour's ghost vector through the
+ *     NVSwitch (pack + send + "unpack" fused; the payload never stops in a send buffer), system-scope fence, then the
+ *     last CTA raises the arrival flag on each neighbour.  The stores drain while the diagonal-block product runs; the
+ *     off-diagonal product is preceded by a one-warp wait on the local flags.  NCCL cannot overlap here because the
+ *     diagonal product is a persistent kernel that fills every SM (its send/recv kernel would queue behind it).
+ *   - ghost vectors are double-buffered by exchange parity and guarded by credits (the receiver tells its senders which
+ *     exchange it has consumed), so non-symmetric neighbour graphs cannot overrun a buffer.
+ *   - allreduce of the Krylov scalars = one tiny kernel: every rank stores its values into every peer's inbox slot,
+ *     fences, stores the sequence number; each rank then sums the slots in rank order (bitwise identical everywhere).
  */
 #include "b200_internal.h"
 #include <dlfcn.h>
@@ -18,6 +28,7 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int);
   ncclResult_t (*CommDestroy)(ncclComm_t);
   ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t);
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t);
   ncclResult_t (*Send)(const void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*Recv)(void *, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t);
   ncclResult_t (*GroupStart)(void);
@@ -25,6 +36,15 @@ struct NcclApi {
   const char *(*GetErrorString)(ncclResult_t);
 };
 static NcclApi g_nccl = {};
+
+struct B200P2P {
+  size_t bytes, bump;                    /* arena size, bump-allocator offset                                       */
+  char  *arena;                          /* this rank's arena                                                       */
+  char  *peer[B200_MAX_RANKS];           /* every rank's arena as mapped here ([rank] == arena)                     */
+  unsigned long long ar_seq;             /* allreduce sequence number (same on all ranks: collective calls)        */
+  unsigned long long **d_inbox;          /* device table: inbox base of every rank                                  */
+};
+#define P2P_CTRL_BYTES ((size_t)2 * B200_MAX_RANKS * P2P_AR_SLOT * 8)   /* allreduce inbox: [parity][sender][slot]  */
 
 static int nccl_load(void)
 {
@@ -34,7 +54,7 @@ static int nccl_load(void)
   if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
   if (!h) return b200_seterr(B200_ERR_LIB, "cannot load libnccl.so.2: %s", dlerror());
 #define SYM(f) do { *(void **)(&g_nccl.f) = dlsym(h, "nccl" #f); if (!g_nccl.f) return b200_seterr(B200_ERR_LIB, "libnccl lacks nccl" #f); } while (0)
-  SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(AllReduce); SYM(Send); SYM(Recv); SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
+  SYM(GetUniqueId); SYM(CommInitRank); SYM(CommDestroy); SYM(AllReduce); SYM(AllGather); SYM(Send); SYM(Recv); SYM(GroupStart); SYM(GroupEnd); SYM(GetErrorString);
 #undef SYM
   g_nccl.h = h;
   return 0;
@@ -80,15 +100,29 @@ extern "C" int b200_comm_rank(int *rank, int *size)
 
 extern "C" int b200_comm_destroy(void)
 {
+  if (g_b200.peer) {
+    B200P2P *P = g_b200.peer;
+    g_b200.p2p = false;
+    cudaDeviceSynchronize();
+    if (g_b200.nccl && g_b200.size > 1) b200_comm_barrier();        /* nobody may still be storing into an arena */
+    for (int r = 0; r < g_b200.size; r++) if (r != g_b200.rank && P->peer[r]) cudaIpcCloseMemHandle(P->peer[r]);
+    cudaFree(P->d_inbox); cudaFree(P->arena);
+    free(P);
+    g_b200.peer = NULL;
+  }
+  g_b200.p2p = false;
   if (g_b200.nccl) { g_nccl.CommDestroy((ncclComm_t)g_b200.nccl); g_b200.nccl = NULL; }
-  g_b200.rank = 0; g_b200.size = 1; g_b200.p2p = false;
+  g_b200.rank = 0; g_b200.size = 1;
   return 0;
 }
+
+static int p2p_allreduce(double *dvals, int n, int op_max);
 
 int b200_comm_allreduce_dev(double *dvals, int n, int op_max)
 {
   if (g_b200.size <= 1) return 0;
   if (!g_b200.nccl) return b200_seterr(B200_ERR_ORDER, "communicator not initialised");
+  if (g_b200.p2p && n <= P2P_AR_MAXV) return p2p_allreduce(dvals, n, op_max);
   B200_NCCL(g_nccl.AllReduce(dvals, dvals, (size_t)n, ncclDouble, op_max ? ncclMax : ncclSum, (ncclComm_t)g_b200.nccl, g_b200.stream));
   return 0;
 }
@@ -109,10 +143,118 @@ extern "C" int b200_comm_barrier(void)
   return 0;
 }
 
+/* ------------------------------------------------------------------------------------------------ peer memory */
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
+{
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
+{
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ void st_relaxed_sys_f64(double *p, double v)
+{
+  asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
+}
+__device__ __forceinline__ double ld_relaxed_sys_f64(const double *p)
+{
+  double v;
+  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
+  return v;
+}
+
+/* one CTA: thread t < size pushes this rank's n values into rank t's inbox, then waits for rank t's values here */
+__global__ void __launch_bounds__(64) p2p_allreduce_kernel(double *vals, int n, int op_max, unsigned long long seq, int rank, int size,
+                                                           unsigned long long *const *__restrict__ inbox)
+{
+  const int t = threadIdx.x;
+  const size_t par = (size_t)(seq & 1ull) * B200_MAX_RANKS * P2P_AR_SLOT;
+  if (t < size) {
+    unsigned long long *slot = inbox[t] + par + (size_t)rank * P2P_AR_SLOT;
+    for (int v = 0; v < n; v++) st_relaxed_sys_f64(reinterpret_cast<double *>(slot) + 1 + v, vals[v]);
+    __threadfence_system();
+    st_release_sys(slot, seq);
+    const unsigned long long *mine = inbox[rank] + par + (size_t)t * P2P_AR_SLOT;
+    while (ld_acquire_sys(mine) != seq) { }
+  }
+  __syncthreads();
+  if (t < n) {
+    const double *base = reinterpret_cast<const double *>(inbox[rank] + par) + 1 + t;
+    double acc = ld_relaxed_sys_f64(base);
+    for (int r = 1; r < size; r++) {
+      const double w = ld_relaxed_sys_f64(base + (size_t)r * P2P_AR_SLOT);
+      acc = op_max ? (w > acc || w != w ? w : acc) : acc + w;                      /* fixed rank order             */
+    }
+    vals[t] = acc;
+  }
+}
+
+static int p2p_allreduce(double *dvals, int n, int op_max)
+{
+  B200Ctx &c = g_b200;
+  B200P2P *P = c.peer;
+  if (n <= 0) return 0;
+  P->ar_seq++;
+  p2p_allreduce_kernel<<<1, 64, 0, c.stream>>>(dvals, n, op_max, P->ar_seq, c.rank, c.size, P->d_inbox);
+  B200_LAUNCHED(1);
+  return 0;
+}
+
+static int p2p_alloc(size_t bytes, size_t *off)
+{
+  B200P2P *P = g_b200.peer;
+  const size_t a = (P->bump + 255) & ~(size_t)255;
+  if (a + bytes > P->bytes) return 1;
+  *off = a; P->bump = a + bytes;
+  return 0;
+}
+
 extern "C" int b200_comm_enable_p2p(int enable)
 {
-  if (enable) return b200_seterr(B200_ERR_SUP, "peer-store transport is not built in this version");
-  g_b200.p2p = false;
+  B200_NEED_INIT();
+  B200Ctx &c = g_b200;
+  if (!enable) {
+    if (c.peer) return b200_seterr(B200_ERR_ARG_WRONGSTATE, "the peer-memory transport stays on until b200_comm_destroy");
+    return 0;
+  }
+  if (c.p2p) return 0;
+  if (c.size <= 1) return 0;
+  if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "b200_comm_enable_p2p needs b200_comm_init first (the handles travel over it)");
+  B200P2P *P = (B200P2P *)calloc(1, sizeof(B200P2P));
+  if (!P) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  size_t mb = 512;
+  const char *e = getenv("B200_P2P_ARENA_MB");
+  if (e && atol(e) > 0) mb = (size_t)atol(e);
+  P->bytes = mb << 20;
+  B200_CUDA(cudaMalloc((void **)&P->arena, P->bytes));
+  B200_CUDA(cudaMemset(P->arena, 0, P->bytes));
+  P->bump = P2P_CTRL_BYTES;
+  /* exchange the IPC handles through the NCCL communicator */
+  cudaIpcMemHandle_t mine, all[B200_MAX_RANKS];
+  B200_CUDA(cudaIpcGetMemHandle(&mine, P->arena));
+  char *dh = NULL;
+  B200_CUDA(cudaMalloc((void **)&dh, sizeof(mine) * (size_t)(c.size + 1)));
+  B200_CUDA(cudaMemcpy(dh, &mine, sizeof(mine), cudaMemcpyHostToDevice));
+  B200_NCCL(g_nccl.AllGather(dh, dh + sizeof(mine), sizeof(mine), ncclChar, (ncclComm_t)c.nccl, c.stream));
+  B200_CUDA(cudaStreamSynchronize(c.stream));
+  B200_CUDA(cudaMemcpy(all, dh + sizeof(mine), sizeof(mine) * (size_t)c.size, cudaMemcpyDeviceToHost));
+  cudaFree(dh);
+  for (int r = 0; r < c.size; r++) {
+    if (r == c.rank) { P->peer[r] = P->arena; continue; }
+    cudaError_t ce = cudaIpcOpenMemHandle((void **)&P->peer[r], all[r], cudaIpcMemLazyEnablePeerAccess);
+    if (ce != cudaSuccess) return b200_seterr(B200_ERR_LIB, "cudaIpcOpenMemHandle for rank %d: %s (no NVLink peer access?)", r, cudaGetErrorString(ce));
+  }
+  unsigned long long *tab[B200_MAX_RANKS];
+  for (int r = 0; r < c.size; r++) tab[r] = reinterpret_cast<unsigned long long *>(P->peer[r]);
+  B200_CUDA(cudaMalloc((void **)&P->d_inbox, sizeof(tab)));
+  B200_CUDA(cudaMemcpy(P->d_inbox, tab, sizeof(void *) * (size_t)c.size, cudaMemcpyHostToDevice));
+  c.peer = P;
+  /* everyone's arena must be zeroed and mapped before the first store lands */
+  B200_CHK(b200_comm_barrier());
+  c.p2p = true;
   return 0;
 }
 
@@ -128,6 +270,161 @@ __global__ void __launch_bounds__(256) pack_kernel(int n, const int *__restrict_
 {
   const int stride = gridDim.x * blockDim.x;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) buf[i] = __ldg(&x[__ldg(&idx[i])]);
+}
+
+/* per-matrix peer plan: where this rank's packed entries go on each neighbour, and the flags/credits around them */
+struct PeerPlanDev {
+  int nto, nfrom;
+  const int *to_starts;                          /* [nto+1]                                                          */
+  double *const *dst;                            /* [2][nto]: neighbour k's ghost-vector window for me, per parity   */
+  unsigned long long *const *rflag;              /* [nto]  arrival flag on neighbour k (its flag[my rank])           */
+  const unsigned long long *const *lcredit;      /* [nto]  local credit written by neighbour k (consumed exchange)   */
+  unsigned long long *const *rcredit;            /* [nfrom] credit slot on sender k (its credit[my rank])            */
+  const unsigned long long *const *lflag;        /* [nfrom] local arrival flag written by sender k                   */
+};
+struct PeerPlan {
+  PeerPlanDev dev;
+  void       *d_blob;                            /* one device allocation behind the tables above                    */
+  size_t      arena_lo, arena_hi;                /* arena range owned by this matrix                                 */
+  unsigned   *d_ticket;
+};
+
+/* VecScatterBegin as one kernel: Pack_1 (vpscat.c:493) + the send + UnPack_1 fused — x[indices[i]] is stored straight
+ * into the neighbour's ghost vector over NVLink.  Before the first store each CTA checks the credits (the neighbour has
+ * consumed the exchange that last used this parity's buffer); CTA 0 also returns this rank's own credits.  After a
+ * system-scope fence the last CTA raises the arrival flags. */
+__global__ void __launch_bounds__(256) pack_put_kernel(int nsend, const int *__restrict__ idx, const double *__restrict__ x,
+                                                       const PeerPlanDev plan, int parity, unsigned long long epoch, unsigned *ticket)
+{
+  __shared__ int s_starts[B200_MAX_RANKS + 1];
+  __shared__ double *s_dst[B200_MAX_RANKS];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x;
+  /* credits first (stream order: this rank's off-diagonal product of exchange epoch-1 is complete), then wait */
+  if (blockIdx.x == 0 && tid < plan.nfrom) st_release_sys(plan.rcredit[tid], epoch - 1);
+  if (tid <= plan.nto) s_starts[tid] = plan.to_starts[tid];
+  if (tid < plan.nto) {
+    s_dst[tid] = plan.dst[parity * plan.nto + tid];
+    while (ld_acquire_sys(plan.lcredit[tid]) + 2 < epoch) { }
+  }
+  __syncthreads();
+  const int stride = gridDim.x * blockDim.x;
+  int k = 0;
+  for (int i = blockIdx.x * blockDim.x + tid; i < nsend; i += stride) {
+    while (i >= s_starts[k + 1]) k++;
+    s_dst[k][i - s_starts[k]] = __ldg(&x[__ldg(&idx[i])]);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (tid == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence_system();
+  if (tid < plan.nto) st_release_sys(plan.rflag[tid], epoch);
+  if (tid == 0) *ticket = 0;
+}
+
+/* VecScatterEnd: one warp waits until every sender's flag shows this exchange */
+__global__ void __launch_bounds__(32) wait_arrivals_kernel(const PeerPlanDev plan, unsigned long long epoch)
+{
+  if ((int)threadIdx.x < plan.nfrom) while (ld_acquire_sys(plan.lflag[threadIdx.x]) < epoch) { }
+}
+
+static void peerplan_free(b200_mat M)
+{
+  PeerPlan *pp = (PeerPlan *)M->peerplan;
+  if (!pp) return;
+  B200P2P *P = g_b200.peer;
+  cudaFree(pp->d_blob); cudaFree(pp->d_ticket);
+  if (P && P->bump == pp->arena_hi) P->bump = pp->arena_lo;      /* last one in: give the arena range back          */
+  free(pp);
+  M->peerplan = NULL;
+  M->d_lvec[0] = M->d_lvec[1] = NULL;                             /* they lived in the arena                          */
+}
+void b200_mpiaij_peer_free(b200_mat M) { peerplan_free(M); }
+
+/* collective: carve the ghost vectors / flags / credits out of the arena and learn where every neighbour put theirs */
+static int peerplan_build(b200_mat M)
+{
+  B200Ctx &c = g_b200;
+  B200P2P *P = c.peer;
+  const int size = c.size, rank = c.rank, nghost = M->nghost;
+  /* meta[r] = { ok, off_lvec0, off_lvec1, off_flag, off_credit, recv_start[0..size) } */
+  const int W = 5 + B200_MAX_RANKS;
+  long long mine[5 + B200_MAX_RANKS], all[B200_MAX_RANKS][5 + B200_MAX_RANKS];
+  const size_t lo = P->bump;
+  size_t o0 = 0, o1 = 0, of = 0, oc = 0;
+  int fail = p2p_alloc(sizeof(double) * (size_t)(nghost + 2), &o0);
+  if (!fail) fail = p2p_alloc(sizeof(double) * (size_t)(nghost + 2), &o1);
+  if (!fail) fail = p2p_alloc(sizeof(unsigned long long) * B200_MAX_RANKS, &of);
+  if (!fail) fail = p2p_alloc(sizeof(unsigned long long) * B200_MAX_RANKS, &oc);
+  const size_t hi = P->bump;
+  mine[0] = fail ? 0 : 1; mine[1] = (long long)o0; mine[2] = (long long)o1; mine[3] = (long long)of; mine[4] = (long long)oc;
+  for (int r = 0; r < B200_MAX_RANKS; r++) mine[5 + r] = -1;
+  for (int k = 0; k < M->nfrom; k++) mine[5 + M->from_procs[k]] = M->from_starts[k];
+  long long *dm = NULL;
+  B200_CUDA(cudaMalloc((void **)&dm, sizeof(long long) * (size_t)W * (size_t)(size + 1)));
+  B200_CUDA(cudaMemcpy(dm, mine, sizeof(mine), cudaMemcpyHostToDevice));
+  B200_NCCL(g_nccl.AllGather(dm, dm + W, (size_t)W, ncclInt64, (ncclComm_t)c.nccl, c.stream));
+  B200_CUDA(cudaStreamSynchronize(c.stream));
+  B200_CUDA(cudaMemcpy(all, dm + W, sizeof(long long) * (size_t)W * (size_t)size, cudaMemcpyDeviceToHost));
+  cudaFree(dm);
+  bool ok = true;
+  for (int r = 0; r < size; r++) ok = ok && all[r][0] == 1;
+  if (!ok) { P->bump = lo; return 1; }                            /* every rank sees the same table -> same decision  */
+  for (int k = 0; k < M->nto; k++)
+    if (all[M->to_procs[k]][5 + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not expect the entries rank %d sends", M->to_procs[k], rank);
+  if (!fail) {
+    B200_CUDA(cudaMemsetAsync(P->arena + o0, 0, sizeof(double) * (size_t)(nghost + 2), c.stream));
+    B200_CUDA(cudaMemsetAsync(P->arena + o1, 0, sizeof(double) * (size_t)(nghost + 2), c.stream));
+    B200_CUDA(cudaMemsetAsync(P->arena + of, 0, sizeof(unsigned long long) * B200_MAX_RANKS, c.stream));
+    B200_CUDA(cudaMemsetAsync(P->arena + oc, 0, sizeof(unsigned long long) * B200_MAX_RANKS, c.stream));
+  }
+  PeerPlan *pp = (PeerPlan *)calloc(1, sizeof(PeerPlan));
+  if (!pp) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  pp->arena_lo = lo; pp->arena_hi = hi;
+  const int nto = M->nto, nfrom = M->nfrom;
+  /* blob layout: to_starts[nto+1] ints (padded to 8 B) | dst[2*nto] | rflag[nto] | lcredit[nto] | rcredit[nfrom] | lflag[nfrom] */
+  const size_t n_int = (size_t)((nto + 1 + 1) & ~1);
+  const size_t nptr = (size_t)(4 * nto + 2 * nfrom);
+  const size_t bytes = n_int * sizeof(int) + nptr * sizeof(void *) + 16;
+  char *hb = (char *)calloc(1, bytes);
+  int *h_starts = (int *)hb;
+  void **hp = (void **)(hb + n_int * sizeof(int));
+  for (int k = 0; k <= nto; k++) h_starts[k] = M->to_starts[k];
+  for (int k = 0; k < nto; k++) {
+    const int q = M->to_procs[k];
+    const long long rs = all[q][5 + rank];
+    hp[0 * nto + k] = P->peer[q] + all[q][1] + 8 * rs;                                  /* dst parity 0 */
+    hp[1 * nto + k] = P->peer[q] + all[q][2] + 8 * rs;                                  /* dst parity 1 */
+    hp[2 * nto + k] = P->peer[q] + all[q][3] + 8 * (size_t)rank;                        /* rflag        */
+    hp[3 * nto + k] = P->arena + oc + 8 * (size_t)q;                                    /* lcredit      */
+  }
+  for (int k = 0; k < nfrom; k++) {
+    const int q = M->from_procs[k];
+    hp[4 * nto + k]         = P->peer[q] + all[q][4] + 8 * (size_t)rank;                /* rcredit      */
+    hp[4 * nto + nfrom + k] = P->arena + of + 8 * (size_t)q;                            /* lflag        */
+  }
+  B200_CUDA(cudaMalloc(&pp->d_blob, bytes));
+  B200_CUDA(cudaMemcpy(pp->d_blob, hb, bytes, cudaMemcpyHostToDevice));
+  free(hb);
+  B200_CUDA(cudaMalloc((void **)&pp->d_ticket, sizeof(unsigned)));
+  B200_CUDA(cudaMemset(pp->d_ticket, 0, sizeof(unsigned)));
+  char *db = (char *)pp->d_blob;
+  void **dp = (void **)(db + n_int * sizeof(int));
+  pp->dev.nto = nto; pp->dev.nfrom = nfrom;
+  pp->dev.to_starts = (const int *)db;
+  pp->dev.dst     = (double *const *)(dp);
+  pp->dev.rflag   = (unsigned long long *const *)(dp + 2 * nto);
+  pp->dev.lcredit = (const unsigned long long *const *)(dp + 3 * nto);
+  pp->dev.rcredit = (unsigned long long *const *)(dp + 4 * nto);
+  pp->dev.lflag   = (const unsigned long long *const *)(dp + 4 * nto + nfrom);
+  M->d_lvec[0] = (double *)(P->arena + o0);
+  M->d_lvec[1] = (double *)(P->arena + o1);
+  M->peerplan = pp;
+  /* the zeroing above must be complete on every rank before anybody's first store can land */
+  B200_CUDA(cudaStreamSynchronize(c.stream));
+  return b200_comm_barrier();
 }
 
 extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
@@ -146,7 +443,12 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
   int rc = b200_seq_upload(&M->A, m, n_local, Ai, Aj, Aa);
   if (!rc) rc = b200_seq_upload(&M->B, m, nghost, Bi, Bj, Ba);
   if (rc) { b200_mat_destroy(M); return rc; }
-  auto dup = [](const int *p, int n) { int *q = (int *)malloc(sizeof(int) * (size_t)(n > 0 ? n : 1)); if (n > 0) memcpy(q, p, sizeof(int) * (size_t)n); return q; };
+  if ((nto > 0 && (!to_procs || !to_starts || !to_indices)) || (nfrom > 0 && (!from_procs || !from_starts)) || (nghost > 0 && !garray)) {
+    b200_mat_destroy(M);
+    return b200_seterr(B200_ERR_ARG_NULL, "null scatter list with nto %d, nfrom %d, nghost %d", nto, nfrom, nghost);
+  }
+  /* a single rank (or a rank without neighbours) may pass NULL lists: the copies are then all-zero */
+  auto dup = [](const int *p, int n) { int *q = (int *)calloc((size_t)(n > 0 ? n : 1), sizeof(int)); if (q && p && n > 0) memcpy(q, p, sizeof(int) * (size_t)n); return q; };
   M->to_procs = dup(to_procs, nto); M->to_starts = dup(to_starts, nto + 1);
   M->from_procs = dup(from_procs, nfrom); M->from_starts = dup(from_starts, nfrom + 1);
   if (nto == 0) M->to_starts[0] = 0;
@@ -154,14 +456,21 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
   const int nsend = M->to_starts[nto];
   if (M->from_starts[nfrom] != nghost) { b200_mat_destroy(M); return b200_seterr(B200_ERR_ARG_SIZ, "receive lists cover %d of %d ghosts", M->from_starts[nfrom], nghost); }
   B200_CUDA(cudaMalloc((void **)&M->d_garray, sizeof(int) * (size_t)(nghost + 1)));
-  B200_CUDA(cudaMalloc((void **)&M->d_lvec[0], sizeof(double) * (size_t)(nghost + 2)));
-  B200_CUDA(cudaMalloc((void **)&M->d_lvec[1], sizeof(double) * (size_t)(nghost + 2)));
+  if (g_b200.p2p && g_b200.size > 1) {
+    /* collective; falls back to the NCCL exchange for this matrix (on every rank alike) when an arena is full */
+    const int prc = peerplan_build(M);
+    if (prc > 1) { b200_mat_destroy(M); return prc; }
+  }
+  if (!M->peerplan) {
+    B200_CUDA(cudaMalloc((void **)&M->d_lvec[0], sizeof(double) * (size_t)(nghost + 2)));
+    B200_CUDA(cudaMalloc((void **)&M->d_lvec[1], sizeof(double) * (size_t)(nghost + 2)));
+    B200_CUDA(cudaMemset(M->d_lvec[0], 0, sizeof(double) * (size_t)(nghost + 2)));
+    B200_CUDA(cudaMemset(M->d_lvec[1], 0, sizeof(double) * (size_t)(nghost + 2)));
+  }
   B200_CUDA(cudaMalloc((void **)&M->d_to_indices, sizeof(int) * (size_t)(nsend + 1)));
   B200_CUDA(cudaMalloc((void **)&M->d_sendbuf, sizeof(double) * (size_t)(nsend + 2)));
   if (nghost) B200_CUDA(cudaMemcpy(M->d_garray, garray, sizeof(int) * (size_t)nghost, cudaMemcpyHostToDevice));
   if (nsend) B200_CUDA(cudaMemcpy(M->d_to_indices, to_indices, sizeof(int) * (size_t)nsend, cudaMemcpyHostToDevice));
-  B200_CUDA(cudaMemset(M->d_lvec[0], 0, sizeof(double) * (size_t)(nghost + 2)));
-  B200_CUDA(cudaMemset(M->d_lvec[1], 0, sizeof(double) * (size_t)(nghost + 2)));
   M->epoch = 0;
   *Aout = M;
   return 0;
@@ -195,6 +504,13 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x)
   if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "MPIAIJ MatMult on %d ranks needs b200_comm_init", c.size);
   const int nsend = A->to_starts[A->nto];
   double *lvec = A->d_lvec[A->epoch & 1];
+  if (A->peerplan) {
+    PeerPlan *pp = (PeerPlan *)A->peerplan;
+    int g = (nsend + 255) / 256; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
+    pack_put_kernel<<<g, 256, 0, c.stream>>>(nsend, A->d_to_indices, x, pp->dev, (int)(A->epoch & 1), (unsigned long long)A->epoch, pp->d_ticket);
+    B200_LAUNCHED(1);
+    return 0;
+  }
   if (nsend) {
     int g = (nsend + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
     pack_kernel<<<g, 256, 0, c.stream>>>(nsend, A->d_to_indices, x, A->d_sendbuf);
@@ -217,6 +533,13 @@ int b200_mpiaij_exchange_end(b200_mat A)
 {
   B200Ctx &c = g_b200;
   if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
+  if (A->peerplan) {
+    if (A->nfrom) {
+      wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->dev, (unsigned long long)A->epoch);
+      B200_LAUNCHED(1);
+    }
+    return 0;
+  }
   B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
   return 0;
 }

@@ -14,6 +14,8 @@
 #define B200_NSM         148           /* B200: 148 SMs; grids are sized in multiples of it                        */
 #define B200_RED_MAXV    32            /* values one reduction launch can produce (VecMDot chunk)                  */
 #define B200_RED_MAXBLK  (B200_NSM * 8)
+#define P2P_AR_SLOT      64            /* u64 words per allreduce inbox slot: sequence number + up to 63 values   */
+#define P2P_AR_MAXV      (P2P_AR_SLOT - 1)
 #define B200_RES_SLOTS   256           /* doubles in the pinned/mapped result buffer                              */
 
 struct B200P2P;                         /* peer-memory state, b200_comm.cu */
@@ -103,6 +105,7 @@ int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_ma
 int b200_comm_allreduce_dev(double *dvals, int n, int op_max);
 int b200_mpiaij_exchange_begin(b200_mat A, const double *x);
 int b200_mpiaij_exchange_end(b200_mat A);
+void b200_mpiaij_peer_free(b200_mat A);
 
 /* reduction grid helper */
 static inline int b200_red_grid(long long n, int threads, int per_thread)

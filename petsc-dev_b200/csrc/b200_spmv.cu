@@ -343,7 +343,13 @@ extern "C" int b200_mat_bytes(b200_mat A, double *b)
 {
   if (!A || !b) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   double v = 12.0 * (double)A->A.nz + 4.0 * ((double)A->A.m + 1) + 8.0 * (double)A->A.n + 8.0 * (double)A->A.m;
-  if (A->kind) v += 12.0 * (double)A->B.nz + 4.0 * ((double)A->B.m + 1) + 8.0 * (double)A->nghost + 16.0 * (double)A->B.m + 16.0 * (double)A->nghost;
+  if (A->kind) {
+    /* off-diagonal MatMultAdd: only the rows it visits count (the non-empty ones when stored compressed: offsets, row
+     * ids, y read + write), the ghost vector once, and the exchange itself (gather read + ghost-vector write) */
+    const double rows = (double)A->B.ncrows;
+    v += 12.0 * (double)A->B.nz + 4.0 * (rows + 1) + (A->B.compressed ? 4.0 * rows : 0.0) + 16.0 * rows + 8.0 * (double)A->nghost
+       + 16.0 * (double)A->nghost;
+  }
   *b = v;
   return 0;
 }
@@ -433,6 +439,7 @@ extern "C" int b200_mat_destroy(b200_mat A)
   b200_seq_free(&A->A);
   if (A->kind) {
     b200_seq_free(&A->B);
+    if (A->peerplan) b200_mpiaij_peer_free(A);
     cudaFree(A->d_garray); cudaFree(A->d_lvec[0]); cudaFree(A->d_lvec[1]); cudaFree(A->d_to_indices); cudaFree(A->d_sendbuf);
     free(A->to_procs); free(A->to_starts); free(A->from_procs); free(A->from_starts);
   }

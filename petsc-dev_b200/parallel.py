@@ -167,3 +167,15 @@ def comm_init(rank, size, dist=None, device=None):
         raw = bytes(t.cpu().numpy().tolist())
         buf = (C.c_ubyte * 128).from_buffer_copy(raw)
     _chk(lib.b200_comm_init(int(rank), int(size), buf), "b200_comm_init")
+
+
+def enable_p2p(rank=None, size=None, dist=None):
+    """Switch the ghost exchange and the scalar allreduces to NVLink peer memory (collective; after comm_init).  The
+    CUDA IPC handles travel over the library's own NCCL communicator, so nothing is needed from the host program."""
+    _chk(lib.b200_comm_enable_p2p(1), "b200_comm_enable_p2p")
+
+
+def p2p_enabled():
+    e = C.c_int()
+    _chk(lib.b200_comm_p2p_enabled(C.byref(e)), "b200_comm_p2p_enabled")
+    return bool(e.value)

@@ -1,0 +1,130 @@
+"""One rank of the real multi-GPU parity run (launched by tests/test_gpu_multi.py through torch.distributed.run, one
+process per GPU, NCCL).  Every rank builds its row slab of the same global matrix, the library exchanges the ghost
+entries GPU to GPU, and rank 0 compares the gathered result with the reference's own sequential kernels applied per
+rank (oracle/mpiaij_restate.mult = MatMult_SeqAIJ on the diagonal block + MatMultAdd_SeqAIJ on the off-diagonal block,
+mpiaij.c:1111-1114) and the KSP residual histories with the reference's KSPSolve on the whole matrix.
+Prints one JSON line on rank 0."""
+import importlib
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    rank, lrank, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+    transport = sys.argv[1] if len(sys.argv) > 1 else "nccl"
+    torch.cuda.set_device(lrank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lrank))
+    pb = importlib.import_module("petsc-dev_b200")
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    P = importlib.import_module("petsc-dev_b200.problems")
+    pb.init(lrank)
+    par.comm_init(rank, world, dist, device="cuda")
+    if transport == "p2p":
+        par.enable_p2p(rank, world, dist)
+    cases = {
+        "lap2d": (40 * 30, 1, lambda r0, r1: P.laplace2d_5pt(40, 30, r0, r1)),
+        "lap7": (24 ** 3, 1, lambda r0, r1: P.laplace3d_7pt(24, r0=r0, r1=r1)),
+        "s27": (16 ** 3, 1, lambda r0, r1: P.stencil3d_27pt(16, r0=r0, r1=r1)),
+        "bs3": (3 * 8 ** 3, 3, lambda r0, r1: P.elasticity_bs3(8, r0=r0, r1=r1)),
+        "plaw": (20000, 1, lambda r0, r1: P.powerlaw(20000, r0, r1, seed=4, xm=4.0, lmax=600)),
+    }
+    out = {"world": world, "transport": transport, "cases": {}}
+    R = None
+    if rank == 0:
+        from oracle import refpetsc as R
+        from oracle import mpiaij_restate as O
+    for name, (N, bs, gen) in cases.items():
+        ranges = par.split_ownership(N, world, bs)
+        rs, re_ = int(ranges[rank]), int(ranges[rank + 1])
+        m = re_ - rs
+        ai, aj, aa = gen(rs, re_)
+        ai = ai - ai[0]
+        lanes = -1 if name == "plaw" else 1           # 1: reference left-to-right row sums -> bit-exact
+        pb.spmv_tuning(lanes_per_row=lanes)
+        try:
+            host = par.setup_mpiaij_host(rank, world, ranges, ai, aj, aa, N, bs=bs, dist=dist, device="cuda")
+            A = par.create_mpiaij(host)
+        finally:
+            pb.spmv_tuning()
+        xh, yh = P.random_vector(N, 2), P.random_vector(N, 3)
+        x, y, z = pb.Vec(m, xh[rs:re_]), pb.Vec(m, yh[rs:re_]), pb.Vec(m)
+
+        def gather(v):
+            mx = int(np.max(np.diff(ranges)))
+            t = torch.zeros(mx, dtype=torch.float64, device="cuda")
+            t[:m] = torch.from_numpy(v.get_array()).cuda()
+            parts = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(parts, t)
+            return np.concatenate([parts[r][: int(ranges[r + 1] - ranges[r])].cpu().numpy() for r in range(world)])
+
+        for _ in range(3):                            # repeated products: the double-buffered ghost vector must stay right
+            A.mult(x, z)
+        got = gather(z)
+        A.mult_add(x, y, z)
+        got_add = gather(z)
+        # vector reductions across ranks
+        dot = x.dot(y)
+        nrm = x.norm()
+        # KSP CG / GMRES on the distributed operator (SPD cases only)
+        ksp = {}
+        if name in ("lap2d", "lap7", "s27", "bs3"):
+            ones = pb.Vec(m); ones.set(1.0)
+            b, sol = pb.Vec(m), pb.Vec(m)
+            A.mult(ones, b)
+            for kt, fused in (("cg", 0), ("cg", 1), ("gmres", 0)):
+                sol.set(0.0)
+                r = pb.ksp_solve(A, b, sol, ksp_type=kt, pc_type="jacobi", rtol=1e-8, fused=fused, check_every=1)
+                ksp["%s_%d" % (kt, fused)] = dict(its=int(r["its"]), reason=int(r["reason"]), history=[float(v) for v in r["history"]],
+                                                  sol=gather(sol).tolist() if N <= 5000 else None)
+        if rank == 0:
+            def gen0(r0, r1):
+                a_i, a_j, a_a = gen(r0, r1)
+                return a_i - a_i[0], a_j, a_a
+            _, S = O.all_structures(world, N, gen0, bs)
+            want = O.mult(R, ranges, S, xh)
+            want_add = O.mult(R, ranges, S, xh, add_y=yh)
+            res = {}
+            if name == "plaw":
+                sc = np.maximum(np.abs(want), 1.0)
+                res["mult_ok"] = bool(np.all(np.abs(got - want) <= 1e-12 * sc))
+                res["multadd_ok"] = bool(np.all(np.abs(got_add - want_add) <= 1e-12 * (sc + np.abs(yh))))
+                res["bit_exact"] = False
+            else:
+                res["mult_ok"] = bool(np.array_equal(got, want))
+                res["multadd_ok"] = bool(np.array_equal(got_add, want_add))
+                res["bit_exact"] = True
+            res["max_abs_err"] = float(np.max(np.abs(got - want)))
+            res["dot_rel"] = float(abs(dot - R.vec_dot(xh, yh)) / abs(R.vec_dot(xh, yh)))
+            res["norm_rel"] = float(abs(nrm - R.vec_norm(xh)) / R.vec_norm(xh))
+            if ksp:
+                fi, fj, fa = gen0(0, N)
+                ref = R.RefMat(N, N, fi, fj, fa, no_inode=True)
+                bh = ref.mult(np.ones(N))
+                for key, r in ksp.items():
+                    kt = key.split("_")[0]
+                    rr = ref.ksp_solve(bh, kt, "jacobi", rtol=1e-8)
+                    k = min(len(r["history"]), len(rr["history"]))
+                    h, hr = np.array(r["history"][:k]), np.array(rr["history"][:k])
+                    # gate: compare while the residual is above 1e-6 of the start (rounding-amplified tail excluded)
+                    gate = hr > 1e-6 * hr[0]
+                    dev = float(np.max(np.abs(h[gate] - hr[gate]) / hr[gate]))
+                    res[key] = dict(its=r["its"], ref_its=int(rr["its"]), reason=r["reason"], ref_reason=int(rr["reason"]), hist_dev=dev)
+            out["cases"][name] = res
+        del A
+    if rank == 0:
+        print("MULTI_GPU_RESULT " + json.dumps(out))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,50 @@
+"""Real multi-GPU parity (needs >= 2 B200s on the box; skipped on a 1-GPU box): one process per GPU over NCCL, the MPIAIJ
+operator with its ghost exchange GPU to GPU, against the reference's sequential kernels applied per rank and the
+reference KSPSolve (tests/multi_gpu_worker.py does the work; this file launches it the way bench.py is launched)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _ngpus():
+    try:
+        out = subprocess.run(["nvidia-smi", "-L"], capture_output=True, text=True, timeout=60).stdout
+        return sum(1 for l in out.splitlines() if l.startswith("GPU "))
+    except Exception:
+        return 0
+
+
+def _launch(world, transport):
+    port = 29500 + (os.getpid() + world * 7 + (13 if transport == "p2p" else 0)) % 400
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "multi_gpu_worker.py"), transport]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=420, cwd=ROOT)
+    assert r.returncode == 0, (r.stdout[-3000:], r.stderr[-5000:])
+    line = [l for l in r.stdout.splitlines() if l.startswith("MULTI_GPU_RESULT ")]
+    assert line, r.stdout[-3000:]
+    return json.loads(line[-1][len("MULTI_GPU_RESULT "):])
+
+
+@pytest.mark.parametrize("transport", ["nccl", "p2p"])
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_mpiaij_across_gpus(world, transport):
+    if _ngpus() < world:
+        pytest.skip("box has fewer than %d GPUs" % world)
+    out = _launch(world, transport)
+    assert out["world"] == world
+    for name, res in out["cases"].items():
+        assert res["mult_ok"] and res["multadd_ok"], (name, res)          # bit-exact for the stencils, 1e-12 for plaw
+        assert res["dot_rel"] < 1e-13 and res["norm_rel"] < 1e-13, (name, res)
+        for key in ("cg_0", "cg_1", "gmres_0"):
+            if key in res:
+                k = res[key]
+                assert abs(k["its"] - k["ref_its"]) <= 1, (name, key, k)      # north_star: iteration counts within +-1
+                assert k["hist_dev"] < 1e-10, (name, key, k)                  # residual histories within 1e-10 relative
+                assert k["reason"] == k["ref_reason"], (name, key, k)
