@@ -21,6 +21,7 @@
 #include "b200_internal.h"
 #include <dlfcn.h>
 #include <nccl.h>
+#include "b200_p2p_dev.cuh"
 
 struct NcclApi {
   void *h;
@@ -145,51 +146,10 @@ extern "C" int b200_comm_barrier(void)
 
 /* ------------------------------------------------------------------------------------------------ peer memory */
 
-__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p)
-{
-  unsigned long long v;
-  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v)
-{
-  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
-}
-__device__ __forceinline__ void st_relaxed_sys_f64(double *p, double v)
-{
-  asm volatile("st.relaxed.sys.global.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory");
-}
-__device__ __forceinline__ double ld_relaxed_sys_f64(const double *p)
-{
-  double v;
-  asm volatile("ld.relaxed.sys.global.f64 %0, [%1];" : "=d"(v) : "l"(p) : "memory");
-  return v;
-}
-
-/* one CTA: thread t < size pushes this rank's n values into rank t's inbox, then waits for rank t's values here */
 __global__ void __launch_bounds__(64) p2p_allreduce_kernel(double *vals, int n, int op_max, unsigned long long seq, int rank, int size,
                                                            unsigned long long *const *__restrict__ inbox)
 {
-  const int t = threadIdx.x;
-  const size_t par = (size_t)(seq & 1ull) * B200_MAX_RANKS * P2P_AR_SLOT;
-  if (t < size) {
-    unsigned long long *slot = inbox[t] + par + (size_t)rank * P2P_AR_SLOT;
-    for (int v = 0; v < n; v++) st_relaxed_sys_f64(reinterpret_cast<double *>(slot) + 1 + v, vals[v]);
-    __threadfence_system();
-    st_release_sys(slot, seq);
-    const unsigned long long *mine = inbox[rank] + par + (size_t)t * P2P_AR_SLOT;
-    while (ld_acquire_sys(mine) != seq) { }
-  }
-  __syncthreads();
-  if (t < n) {
-    const double *base = reinterpret_cast<const double *>(inbox[rank] + par) + 1 + t;
-    double acc = ld_relaxed_sys_f64(base);
-    for (int r = 1; r < size; r++) {
-      const double w = ld_relaxed_sys_f64(base + (size_t)r * P2P_AR_SLOT);
-      acc = op_max ? (w > acc || w != w ? w : acc) : acc + w;                      /* fixed rank order             */
-    }
-    vals[t] = acc;
-  }
+  b200_p2p_allreduce_cta(vals, n, op_max, seq, rank, size, inbox);
 }
 
 static int p2p_allreduce(double *dvals, int n, int op_max)
@@ -201,6 +161,15 @@ static int p2p_allreduce(double *dvals, int n, int op_max)
   p2p_allreduce_kernel<<<1, 64, 0, c.stream>>>(dvals, n, op_max, P->ar_seq, c.rank, c.size, P->d_inbox);
   B200_LAUNCHED(1);
   return 0;
+}
+
+/* the fused CG folds the allreduce into its own scalar kernels: hand out the next sequence number and the inbox table */
+bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox)
+{
+  if (!g_b200.p2p || !g_b200.peer) return false;
+  *seq = ++g_b200.peer->ar_seq;
+  *inbox = g_b200.peer->d_inbox;
+  return true;
 }
 
 static int p2p_alloc(size_t bytes, size_t *off)

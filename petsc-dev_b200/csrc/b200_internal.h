@@ -99,6 +99,8 @@ struct b200_mat_s {
 int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
+int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);
+int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out);
 
 /* internal cross-file entry points */
 int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_max /*0 sum, 1 max*/);
@@ -106,6 +108,7 @@ int b200_comm_allreduce_dev(double *dvals, int n, int op_max);
 int b200_mpiaij_exchange_begin(b200_mat A, const double *x);
 int b200_mpiaij_exchange_end(b200_mat A);
 void b200_mpiaij_peer_free(b200_mat A);
+bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox);
 
 /* reduction grid helper */
 static inline int b200_red_grid(long long n, int threads, int per_thread)

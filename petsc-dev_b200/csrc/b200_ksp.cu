@@ -18,6 +18,7 @@
  *              residual history).  The host only polls the reason every `check_every` iterations.
  */
 #include "b200_internal.h"
+#include "b200_p2p_dev.cuh"
 #include <math.h>
 #include <vector>
 
@@ -193,8 +194,12 @@ __device__ void cg_top(CgState *s)
 __global__ void cg_begin_kernel(CgState *s) { if (threadIdx.x == 0 && s->reason == 0) cg_top(s); }
 
 /* after p.w is known (cg.c:207-220) */
-__global__ void cg_after_dot_kernel(CgState *s)
+struct CgAr { unsigned long long seq; unsigned long long *const *inbox; int rank, size; };   /* size <= 1: no allreduce */
+
+__global__ void __launch_bounds__(64) cg_after_dot_kernel(CgState *s, const CgAr ar)
 {
+  /* the allreduce is unconditional (collective): every rank runs the same number of them whatever s->reason says */
+  if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[3], 1, 0, ar.seq, ar.rank, ar.size, ar.inbox);
   if (threadIdx.x != 0 || s->reason != 0) return;
   s->dpi = s->red[3];
   s->betaold = s->beta;
@@ -204,8 +209,9 @@ __global__ void cg_after_dot_kernel(CgState *s)
 }
 
 /* after the update kernel's reductions (cg.c:227-281): norm, history, KSPDefaultConverged, new beta, next top */
-__global__ void cg_after_update_kernel(CgState *s, double *hist)
+__global__ void __launch_bounds__(64) cg_after_update_kernel(CgState *s, double *hist, const CgAr ar)
 {
+  if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[0], 3, 0, ar.seq, ar.rank, ar.size, ar.inbox);
   if (threadIdx.x != 0 || s->reason != 0) return;
   double dp, beta = s->beta;
   if (s->normtype == B200_KSP_NORM_PRECONDITIONED) dp = sqrt(s->red[0]);
@@ -437,6 +443,7 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
 
   const bool seq = (A->kind == 0) && !A->A.compressed && (A->A.m == A->A.n);
   const bool multi = c.size > 1;
+  const bool mpi_dot = (A->kind == 1) && !A->A.compressed && (A->A.m == A->A.n) && A->A.m > 0;
   int gp = ((n + 1) / 2 + 255) / 256; if (gp > B200_NSM * 16) gp = B200_NSM * 16; if (gp < 1) gp = 1;
   const int gu = b200_red_grid((n + 1) / 2, 512, 2);
   if (check_every < 1) check_every = 1;
@@ -447,20 +454,29 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
     for (int k = 0; k < batch; k++) {
       cg_pupdate_kernel<<<gp, 256, 0, st>>>(n, ds, P, Z);
       B200_LAUNCHED(1);
+      CgAr ar1 = {0, NULL, c.rank, 1}, ar2 = {0, NULL, c.rank, 1};
       if (seq) { rc = b200_seq_mult(&A->A, P, NULL, W, false, &ds->red[3]); if (rc) goto done; }
+      else if (mpi_dot) { rc = b200_mpiaij_mult_dot(A, P, W, &ds->red[3]); if (rc) goto done; }
       else {
         rc = op_mult(A, P, W); if (rc) goto done;
         cg_dot_kernel<<<b200_red_grid(n, 512, 4), 512, 0, st>>>(n, ds, P, W, c.d_partials, c.d_ticket, &ds->red[3]);
         B200_LAUNCHED(1);
       }
-      if (multi) { rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done; }
-      cg_after_dot_kernel<<<1, 32, 0, st>>>(ds);
+      /* allreduce of p.w: folded into the scalar kernel over peer memory, else NCCL */
+      if (multi) {
+        if (b200_p2p_next(&ar1.seq, &ar1.inbox)) ar1.size = c.size;
+        else { rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done; }
+      }
+      cg_after_dot_kernel<<<1, 64, 0, st>>>(ds, ar1);
       B200_LAUNCHED(1);
       if (pc->type == 1) cg_update_kernel<true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket);
       else               cg_update_kernel<false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket);
       B200_LAUNCHED(1);
-      if (multi) { rc = b200_comm_allreduce_dev(&ds->red[0], 3, 0); if (rc) goto done; }
-      cg_after_update_kernel<<<1, 32, 0, st>>>(ds, dhist);
+      if (multi) {
+        if (b200_p2p_next(&ar2.seq, &ar2.inbox)) ar2.size = c.size;
+        else { rc = b200_comm_allreduce_dev(&ds->red[0], 3, 0); if (rc) goto done; }
+      }
+      cg_after_update_kernel<<<1, 64, 0, st>>>(ds, dhist, ar2);
       B200_LAUNCHED(1);
     }
     launched += batch;

@@ -38,11 +38,12 @@ static const SpmvCfg g_cfgs[] = {
 static int g_tune_cfg = -1, g_tune_G = -1, g_tune_long = -1, g_tune_park = -1;
 
 /* deterministic final pass over the per-CTA partials of the fused dot */
-__global__ void __launch_bounds__(1024) dot_final_kernel(int n, const double *__restrict__ part, double *out)
+__global__ void __launch_bounds__(1024) dot_final_kernel(int n, const double *__restrict__ part, int n2, const double *__restrict__ part2, double *out)
 {
   __shared__ double s_red[32];
   double s = 0.0;
   for (int i = threadIdx.x; i < n; i += 1024) s += part[i];
+  for (int i = threadIdx.x; i < n2; i += 1024) s += part2[i];
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -214,14 +215,14 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
 
 /* ---- tile-kernel dispatch: (launch shape) x (lanes per row) x (add, dot) */
 template <int G, bool PARK, int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
 {
   const size_t smem = SpmvSmem<THREADS, TILE_NNZ, STAGES>::BYTES;
 #define GO(ADD, DOT) do { \
     auto kern = spmv_tile_kernel<G, PARK, ADD, DOT, THREADS, TILE_NNZ, STAGES>; \
     static bool attr_done = false; \
     if (!attr_done) { cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; attr_done = true; } \
-    kern<<<S->grid, THREADS, smem, st>>>(S->ntiles, S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart, S->d_longpart); \
+    kern<<<S->grid, THREADS, smem, st>>>(S->ntiles, S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart, S->d_longpart, dotx); \
   } while (0)
   if (add) { if (dot) GO(true, true); else GO(true, false); }
   else     { if (dot) GO(false, true); else GO(false, false); }
@@ -230,44 +231,46 @@ static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const doub
 }
 
 template <int G, int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile4(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+static cudaError_t launch_tile4(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
 {
-  return S->park ? launch_tile5<G, true, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st)
-                 : launch_tile5<G, false, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+  return S->park ? launch_tile5<G, true, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st)
+                 : launch_tile5<G, false, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
 }
 
 template <int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile3(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+static cudaError_t launch_tile3(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
 {
   switch (S->G) {
-    case 1:  return launch_tile4<1,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
-    case 2:  return launch_tile4<2,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
-    case 4:  return launch_tile4<4,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
-    case 8:  return launch_tile4<8,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
-    case 16: return launch_tile4<16, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
-    default: return launch_tile4<32, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, st);
+    case 1:  return launch_tile4<1,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    case 2:  return launch_tile4<2,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    case 4:  return launch_tile4<4,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    case 8:  return launch_tile4<8,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    case 16: return launch_tile4<16, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    default: return launch_tile4<32, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
   }
 }
 
-static cudaError_t launch_tile(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, cudaStream_t st)
+static cudaError_t launch_tile(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
 {
   switch (S->cfg) {                       /* must mirror g_cfgs[] */
-    case 0:  return launch_tile3<256, 2048, 1>(S, add, dot, x, yin, z, st);
-    case 1:  return launch_tile3<256, 2048, 2>(S, add, dot, x, yin, z, st);
-    case 2:  return launch_tile3<512, 4096, 2>(S, add, dot, x, yin, z, st);
-    case 3:  return launch_tile3<128, 1024, 1>(S, add, dot, x, yin, z, st);
-    case 4:  return launch_tile3<512, 4096, 1>(S, add, dot, x, yin, z, st);
-    case 5:  return launch_tile3<256, 1792, 2>(S, add, dot, x, yin, z, st);
-    case 6:  return launch_tile3<256, 4096, 2>(S, add, dot, x, yin, z, st);
-    default: return launch_tile3<384, 3072, 1>(S, add, dot, x, yin, z, st);
+    case 0:  return launch_tile3<256, 2048, 1>(S, add, dot, x, yin, z, dotx, st);
+    case 1:  return launch_tile3<256, 2048, 2>(S, add, dot, x, yin, z, dotx, st);
+    case 2:  return launch_tile3<512, 4096, 2>(S, add, dot, x, yin, z, dotx, st);
+    case 3:  return launch_tile3<128, 1024, 1>(S, add, dot, x, yin, z, dotx, st);
+    case 4:  return launch_tile3<512, 4096, 1>(S, add, dot, x, yin, z, dotx, st);
+    case 5:  return launch_tile3<256, 1792, 2>(S, add, dot, x, yin, z, dotx, st);
+    case 6:  return launch_tile3<256, 4096, 2>(S, add, dot, x, yin, z, dotx, st);
+    default: return launch_tile3<384, 3072, 1>(S, add, dot, x, yin, z, dotx, st);
   }
 }
 
-/* z = (add ? yin : 0) + S x ; dot_out (device scalar) receives x.z when non-NULL (needs m == n, all rows visited) */
-int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out)
+/* z = (add ? yin : 0) + S x.  want_dot: the CTAs leave partials of dotx . (z - yin) in S->d_dotpart (dotx NULL = x);
+ * dot_out (device scalar), when non-NULL, receives their sum (one more tiny kernel). */
+int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out)
 {
   cudaStream_t st = g_b200.stream;
   if (S->m == 0) return 0;
+  if (!dotx) dotx = x;
   if (add && z != yin && S->compressed) {
     /* rows the compressed list skips keep y (aij.c:1313-1315) */
     B200_CUDA(cudaMemcpyAsync(z, yin, sizeof(double) * (size_t)S->m, cudaMemcpyDeviceToDevice, st));
@@ -276,24 +279,47 @@ int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *
     zero_rows_kernel<<<B200_NSM * 4, 256, 0, st>>>(S->m, z);
     B200_LAUNCHED(1);
   }
-  if (dot_out && S->compressed) return b200_seterr(B200_ERR_SUP, "fused dot needs an uncompressed square block");
+  if (want_dot && S->compressed && !add) return b200_seterr(B200_ERR_SUP, "fused dot needs an uncompressed block (or the MatMultAdd form)");
   if (S->ntiles) {
-    B200_CUDA(launch_tile(S, add, dot_out != NULL, x, yin, z, st));
+    B200_CUDA(launch_tile(S, add, want_dot, x, yin, z, dotx, st));
     B200_LAUNCHED(1);
   }
   if (S->nlong) {
     double *dp = S->d_dotpart + S->grid;
     const int fg = (S->nlong + 127) / 128;
-#define FIN(ADD, DOT) spmv_long_finish_kernel<ADD, DOT><<<fg, 128, 0, st>>>(S->nlong, S->d_long, S->d_longstart, S->d_rindex, S->d_longpart, x, yin, z, dp)
-    if (add) { if (dot_out) FIN(true, true); else FIN(true, false); }
-    else     { if (dot_out) FIN(false, true); else FIN(false, false); }
+#define FIN(ADD, DOT) spmv_long_finish_kernel<ADD, DOT><<<fg, 128, 0, st>>>(S->nlong, S->d_long, S->d_longstart, S->d_rindex, S->d_longpart, dotx, yin, z, dp)
+    if (add) { if (want_dot) FIN(true, true); else FIN(true, false); }
+    else     { if (want_dot) FIN(false, true); else FIN(false, false); }
 #undef FIN
     B200_LAUNCHED(1);
   }
-  if (dot_out) {
-    dot_final_kernel<<<1, 1024, 0, st>>>(S->grid + S->nlong, S->d_dotpart, dot_out);
+  if (want_dot && dot_out) {
+    dot_final_kernel<<<1, 1024, 0, st>>>((S->ntiles ? S->grid : 0) + S->nlong, S->ntiles ? S->d_dotpart : S->d_dotpart + S->grid, 0, NULL, dot_out);
     B200_LAUNCHED(1);
   }
+  return 0;
+}
+
+int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out)
+{
+  return b200_seq_mult_ex(S, x, yin, z, add, dot_out != NULL, NULL, dot_out);
+}
+
+/* y = A x on the row-partitioned operator with the LOCAL part of x . y left in dot_out (device scalar): the diagonal
+ * block contributes x . (A_d x), the off-diagonal MatMultAdd x . (B lvec); one final kernel adds both partial lists. */
+int b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out)
+{
+  const B200Seq *Sa = &A->A, *Sb = &A->B;
+  if (Sa->compressed || Sa->m != Sa->n) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square, uncompressed diagonal block");
+  B200_CHK(b200_mpiaij_exchange_begin(A, x));
+  B200_CHK(b200_seq_mult_ex(Sa, x, NULL, y, false, true, x, NULL));
+  B200_CHK(b200_mpiaij_exchange_end(A));
+  B200_CHK(b200_seq_mult_ex(Sb, A->d_lvec[A->epoch & 1], y, y, true, true, x, NULL));
+  if (Sa->m == 0) return 0;
+  const int na = (Sa->ntiles ? Sa->grid : 0) + Sa->nlong, nb = (Sb->ntiles ? Sb->grid : 0) + Sb->nlong;
+  dot_final_kernel<<<1, 1024, 0, g_b200.stream>>>(na, Sa->ntiles ? Sa->d_dotpart : Sa->d_dotpart + Sa->grid,
+                                                  nb, Sb->ntiles ? Sb->d_dotpart : Sb->d_dotpart + Sb->grid, dot_out);
+  B200_LAUNCHED(1);
   return 0;
 }
 

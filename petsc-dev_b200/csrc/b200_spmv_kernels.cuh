@@ -72,8 +72,11 @@ template <int G, bool PARK, bool ADD, bool DOT, int THREADS, int TILE_NNZ, int S
 __global__ void __launch_bounds__(THREADS)
 spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
                  const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
-                 const double *yin, double *z, double *__restrict__ dotpart, double *__restrict__ longpart)
+                 const double *yin, double *z, double *__restrict__ dotpart, double *__restrict__ longpart,
+                 const double *__restrict__ dotx)
 {
+  /* DOT: the CTA leaves its share of dotx . (z - yin) in dotpart (dotx == x, yin == 0 for the plain MatMult; for the
+   * off-diagonal MatMultAdd dotx is the LOCAL vector, so that diag + off-diag partials add up to x . (A x)) */
   constexpr int SE = TILE_NNZ + SPMV_ALIGN_PAD;
   extern __shared__ __align__(128) unsigned char spmv_smem[];
   double   *s_a  = reinterpret_cast<double *>(spmv_smem);
@@ -185,7 +188,11 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
               for (int k = b_cur; k < e_cur; k++) sum += sa[k] * __ldg(&x[sj[k]]);
             }
             z[row_cur] = sum;
-            if (DOT) dot += __ldg(&x[row_cur]) * sum;
+            if (DOT) {
+              const double xd = __ldg(&dotx[row_cur]);
+              dot += xd * sum;
+              if (ADD) dot -= xd * y_cur;
+            }
           }
         } else {
           /* lanes without a row have b == e == 0 and fall through to the (warp-converged) shuffles */
@@ -201,9 +208,9 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
 #pragma unroll
           for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
           if (g == 0 && row_cur >= 0) {
+            if (DOT) dot += __ldg(&dotx[row_cur]) * sum;
             if (ADD) sum = y_cur + sum;
             z[row_cur] = sum;
-            if (DOT) dot += __ldg(&x[row_cur]) * sum;
           }
         }
       }
@@ -237,7 +244,7 @@ template <bool ADD, bool DOT>
 __global__ void __launch_bounds__(128)
 spmv_long_finish_kernel(int nlong, const int *__restrict__ longrows, const int *__restrict__ longstart,
                         const int *__restrict__ rindex, const double *__restrict__ longpart,
-                        const double *__restrict__ x, const double *yin, double *z, double *__restrict__ dotpart)
+                        const double *__restrict__ dotx, const double *yin, double *z, double *__restrict__ dotpart)
 {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= nlong) return;
@@ -247,7 +254,7 @@ spmv_long_finish_kernel(int nlong, const int *__restrict__ longrows, const int *
   for (int c = __ldg(&longstart[i]); c < __ldg(&longstart[i + 1]); c++) v += longpart[c];
   const double out = ADD ? yin[row] + v : v;
   z[row] = out;
-  if (DOT) dotpart[i] = __ldg(&x[row]) * out;
+  if (DOT) dotpart[i] = __ldg(&dotx[row]) * v;
 }
 
 #endif /* B200_SPMV_KERNELS_CUH */
