@@ -37,6 +37,23 @@ PetscErrorCode PetscB200Register(void)
     device = rank % ndev;
   }
   if (b200_init((int)device)) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_init(%D) failed: %s",device,b200_last_error());
+  /* more than one rank: the library's own rank-to-rank transport (ghost exchange GPU to GPU inside MatMult_MPIAIJB200).
+     The NCCL id is made on rank 0 and broadcast over PETSC_COMM_WORLD; -b200_p2p 0 keeps the NCCL transport instead of
+     the NVLink peer-memory one.  Not exercised on this box (its only PETSc is the one-rank MPIUNI build). */
+  {
+    PetscMPIInt size;
+    PetscBool   p2p = PETSC_TRUE;
+    char        id[B200_COMM_ID_BYTES];
+    ierr = MPI_Comm_size(PETSC_COMM_WORLD,&size);CHKERRQ(ierr);
+    if (size > 1) {
+      ierr = PetscMemzero(id,sizeof(id));CHKERRQ(ierr);
+      if (!rank && b200_comm_get_unique_id(id)) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_comm_get_unique_id: %s",b200_last_error());
+      ierr = MPI_Bcast(id,B200_COMM_ID_BYTES,MPI_CHAR,0,PETSC_COMM_WORLD);CHKERRQ(ierr);
+      if (b200_comm_init((int)rank,(int)size,id)) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_comm_init: %s",b200_last_error());
+      ierr = PetscOptionsGetBool(PETSC_NULL,"-b200_p2p",&p2p,PETSC_NULL);CHKERRQ(ierr);
+      if (p2p && b200_comm_enable_p2p(1)) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_comm_enable_p2p: %s",b200_last_error());
+    }
+  }
   ierr = VecRegister(VECSEQB200,0,"VecCreate_SeqB200",VecCreate_SeqB200);CHKERRQ(ierr);
   ierr = VecRegister(VECMPIB200,0,"VecCreate_MPIB200",VecCreate_MPIB200);CHKERRQ(ierr);
   ierr = VecRegister(VECB200,   0,"VecCreate_B200",   VecCreate_B200);CHKERRQ(ierr);
