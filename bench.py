@@ -75,6 +75,56 @@ def env_rank():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+def _ref_slab_worker(rank, nprocs, nx, reps, warm, barrier, q):
+    """One host core: the reference's MatMult_SeqAIJ (oracle/_ref, unmodified aij.c:1225) on this core's row slab of the
+    7-pt matrix (rows split like PetscSplitOwnership; global column ids, so x is the whole vector as lvec+local would
+    be).  All cores start together; returns the average seconds per MatMult on this core."""
+    try:
+        from oracle import refpetsc as R
+        P = importlib.import_module("petsc-dev_b200.problems")
+        N = nx ** 3
+        r0 = rank * (N // nprocs) + min(rank, N % nprocs)
+        r1 = r0 + N // nprocs + (1 if rank < N % nprocs else 0)
+        ai, aj, aa = P.laplace3d_7pt(nx, r0=r0, r1=r1)
+        A = R.RefMat(r1 - r0, N, ai - ai[0], aj, aa)
+        x = P.random_vector(N, 2)
+        if warm:
+            A.mult(x, reps=warm)
+        barrier.wait()
+        t0 = time.perf_counter()
+        A.mult(x, reps=reps)
+        dt = (time.perf_counter() - t0) / reps
+        barrier.wait()
+        q.put((rank, dt, int(len(aa)), r1 - r0))
+    except Exception as e:                                  # report, never hang the other cores
+        try:
+            barrier.abort()
+        except Exception:
+            pass
+        q.put((rank, None, repr(e), 0))
+
+
+def reference_all_cores(nx, reps, warm=1, nprocs=None):
+    """The reference CPU MatMult on all host cores of this box: one process per core, each with the unmodified reference
+    kernel on its row slab (what MPIAIJ's ranks would each do, minus the ghost exchange this box has no MPI for).
+    Returns (GB/s aggregate, cores, seconds per MatMult = slowest core)."""
+    import multiprocessing as mp
+    nprocs = nprocs or len(os.sched_getaffinity(0))
+    ctx = mp.get_context("spawn")            # the parent may hold a CUDA context: never fork it
+    barrier, q = ctx.Barrier(nprocs), ctx.Queue()
+    procs = [ctx.Process(target=_ref_slab_worker, args=(r, nprocs, nx, reps, warm, barrier, q)) for r in range(nprocs)]
+    [p.start() for p in procs]
+    res = [q.get(timeout=900) for _ in procs]
+    [p.join(60) for p in procs]
+    bad = [r for r in res if r[1] is None]
+    if bad:
+        raise RuntimeError("reference worker failed: %s" % (bad[0][2],))
+    N = nx ** 3
+    nz = sum(r[2] for r in res)
+    tmax = max(r[1] for r in res)
+    return spmv_bytes(nz, N, N) / tmax / 1e9, nprocs, tmax
+
+
 def run_reference(args):
     """The reference's own CPU implementation (unmodified MatMult_SeqAIJ, src/mat/impls/aij/seq/aij.c:1225, built in
     oracle/_ref) on the host cores; one MPIUNI rank = one core (no MPI exists on this box)."""
@@ -85,29 +135,32 @@ def run_reference(args):
     P = importlib.import_module("petsc-dev_b200.problems")
     nx = args.nx
     N = nx ** 3
+    # all host cores first (forked before this process holds the big matrix)
+    gbs_all, cores, t_all = reference_all_cores(nx, reps=max(args.steps, 1), warm=max(args.warmup, 1))
     ip, j, a = P.laplace3d_7pt(nx)
     A = R.RefMat(N, N, ip, j, a)
     x = P.random_vector(N, 2)
-    for _ in range(args.warmup):
-        A.mult(x)
+    A.mult(x)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        A.mult(x)
-    dt = (time.perf_counter() - t0) / args.steps
+    reps1 = min(args.steps, 5)
+    A.mult(x, reps=reps1)
+    dt1 = (time.perf_counter() - t0) / reps1
     B = spmv_bytes(len(a), N, N)
     b = A.mult(np.ones(N))
     cg_its = min(args.cg_iters, 20)
     r = A.ksp_solve(b, "cg", "jacobi", rtol=1e-50, maxit=cg_its)
-    gbs = B / dt / 1e9
-    line = {"impl": "reference", "metric": METRIC, "value": gbs, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+    line = {"impl": "reference", "metric": METRIC, "value": gbs_all, "unit": "GB/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_all * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": "configs[1]: 3D 7-point Laplacian %d^3, AIJ MatMult (+KSPCG/Jacobi)" % nx, "rows": N,
                        "nnz": int(len(a)), "l2_policy": "inputs (1.7 GB) larger than cache"},
-            "cpu_baseline": {"value": gbs, "unit": "GB/s", "cores": 1, "kind": "reference",
-                             "sample": "full %d^3 matrix, %d MatMult reps; KSPCG %d iterations" % (nx, args.steps, cg_its)},
-            "kspcg": {"iter_per_s": r["its"] / r["seconds"], "iterations": r["its"]},
-            "e2e": {"value": gbs, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            "cpu_baseline": {"value": gbs_all, "unit": "GB/s", "cores": cores, "kind": "reference",
+                             "sample": "full %d^3 matrix, %d MatMult reps, one process per host core each running the "
+                                       "unmodified reference MatMult_SeqAIJ on its row slab" % (nx, args.steps),
+                             "one_core": {"value": B / dt1 / 1e9, "ms_per_step": dt1 * 1e3}},
+            "kspcg": {"iter_per_s": r["its"] / r["seconds"], "iterations": r["its"], "cores": 1,
+                      "note": "reference KSPSolve_CG + PCJACOBI, one MPIUNI rank (no MPI on this box)"},
+            "e2e": {"value": gbs_all, "unit": "GB/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
 
 
@@ -223,12 +276,61 @@ def run_b200(args):
     e2e_val = Btot / (ms_e2e * 1e-3) / 1e9
     checksum = float(np.abs(hy).sum())
 
+    # ---------------- optional: KSPCG strong scaling on a FIXED global grid (north_star: 512^3 7-pt, 1 -> 8 GPUs) ----------------
+    strong = None
+    if args.strong_nx:
+        del A, x, y, one, b, sol, hx, hy
+        snx = args.strong_nx
+        SN = snx ** 3
+        if world == 1:
+            ip, j, a = P.laplace3d_7pt(snx)
+            SA = pb.Mat.from_csr(SN, SN, ip, j, a)
+            sm, sB = SN, spmv_bytes(len(a), SN, SN)
+            del ip, j, a
+        else:
+            sr = par.split_ownership(SN, world)
+            ai, aj, aa = P.laplace3d_7pt(snx, r0=int(sr[rank]), r1=int(sr[rank + 1]))
+            sh = par.setup_mpiaij_host(rank, world, sr, ai - ai[0], aj, aa, SN, dist=dist, device="cuda")
+            SA = par.create_mpiaij(sh)
+            sm, sB = sh["m"], SA.bytes()
+            del ai, aj, aa, sh
+        so, sb, ss = pb.Vec(sm), pb.Vec(sm), pb.Vec(sm)
+        so.set(1.0)
+        SA.mult(so, sb)
+        pb.ksp_solve(SA, sb, ss, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=5, fused=1, histmax=0)
+        barrier()
+        r = pb.ksp_solve(SA, sb, ss, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=args.cg_iters, fused=1,
+                         check_every=args.cg_iters, histmax=0)
+        t = maxr(r["solve_ms"])
+        for _ in range(3):
+            SA.mult(so, sb)
+        barrier()
+        pb.timer_start()
+        for _ in range(20):
+            SA.mult(so, sb)
+        tm = maxr(pb.timer_stop()) / 20
+        sBt = sB
+        if dist is not None:
+            import torch
+            tt = torch.tensor([sB], dtype=torch.float64, device="cuda")
+            dist.all_reduce(tt)
+            sBt = float(tt.item())
+        strong = {"grid": "%d^3 7-pt, fixed total size" % snx, "rows": SN, "iter_per_s": r["its"] / (t * 1e-3),
+                  "ms_per_iter": t / max(r["its"], 1), "iterations": r["its"], "matmult_ms": tm,
+                  "matmult_gbs_total": sBt / (tm * 1e-3) / 1e9,
+                  "cg_gbs_vs_Bcg_min": (sBt + 88.0 * SN) / (t / max(r["its"], 1) * 1e-3) / 1e9}
+
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic = None                       # dram bytes of the dominant kernel from the committed `ncu --set full` capture
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))["spmv_tile_kernel_lap7_256"]["dram_bytes"]
+    except Exception:
+        pass
     per_gpu = (B_alg / (ms_step * 1e-3) / 1e9)
     if rank != 0:
         if dist is not None:
@@ -243,25 +345,21 @@ def run_b200(args):
                        "l2_policy": "inputs (1.7 GB per GPU) larger than the 126 MB L2; no flush"},
             "gflops": (2.0 * nz * world - m * world) / (ms_step * 1e-3) / 1e9,
             "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
-                         "traffic": None, "kernel": "spmv_tile_kernel<G=1,PARK=0,ADD=0,DOT=0,256,2048,1>",
+                         "traffic": traffic, "kernel": "spmv_tile_kernel<G=1,PARK=0,ADD=0,DOT=0,256,2048,1>",
                          "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
                          "algorithmic_bytes_per_launch": B_alg},
             "kspcg": ksp,
+            **({"kspcg_strong": strong} if strong else {}),
             "e2e": {"value": e2e_val, "unit": "GB/s", "h2d_bytes_per_step": 8 * m * world, "d2h_bytes_per_step": 8 * m * world,
                     "ms_per_step": ms_e2e, "checksum": checksum},
             "gpu_launches": int(launches), "clocks": clk, "setup_s": t_setup}
     # CPU baseline on rank 0 at N = 1 only: the reference library on a bounded sample of the same workload
     if world == 1 and not args.no_cpu_baseline:
         try:
-            from oracle import refpetsc as R
-            snx = min(nx, 128)
-            ip, j, a = P.laplace3d_7pt(snx)
-            ref = R.RefMat(snx ** 3, snx ** 3, ip, j, a)
-            xs = P.random_vector(snx ** 3, 2)
-            _, tmin = ref.mult(xs, reps=10, want_time=True)
-            line["cpu_baseline"] = {"value": spmv_bytes(len(a), snx ** 3, snx ** 3) / tmin / 1e9, "unit": "GB/s", "cores": 1,
-                                    "kind": "reference",
-                                    "sample": "reference MatMult_SeqAIJ (oracle/_ref, 1 MPIUNI rank) on the %d^3 7-pt matrix, min of 10" % snx}
+            gbs_all, cores, t_all = reference_all_cores(nx, reps=5, warm=1)
+            line["cpu_baseline"] = {"value": gbs_all, "unit": "GB/s", "cores": cores, "kind": "reference", "ms_per_step": t_all * 1e3,
+                                    "sample": "unmodified reference MatMult_SeqAIJ (oracle/_ref), full %d^3 7-pt matrix row-split "
+                                              "over %d host processes (one per core), 5 reps after 1 warm-up" % (nx, cores)}
         except Exception as e:                       # the checker is absent: report it, never substitute
             line["cpu_baseline"] = {"value": None, "unit": "GB/s", "cores": 0, "kind": "reference", "sample": "unavailable: %s" % e}
     print(json.dumps(line))
@@ -278,6 +376,8 @@ def main():
     ap.add_argument("--nx", type=int, default=256)
     ap.add_argument("--cg-iters", type=int, default=100)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strong-nx", type=int, default=0,
+                    help="also time KSPCG on a FIXED nx^3 7-pt grid split over the ranks (strong scaling; north_star uses 512)")
     ap.add_argument("--transport", default="p2p", choices=["p2p", "nccl"],
                     help="N > 1: ghost exchange + scalar allreduces over NVLink peer memory (own kernels) or NCCL")
     args = ap.parse_args()

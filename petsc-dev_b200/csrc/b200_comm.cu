@@ -211,6 +211,25 @@ extern "C" int b200_comm_enable_p2p(int enable)
   B200_CUDA(cudaStreamSynchronize(c.stream));
   B200_CUDA(cudaMemcpy(all, dh + sizeof(mine), sizeof(mine) * (size_t)c.size, cudaMemcpyDeviceToHost));
   cudaFree(dh);
+  /* the kernels of this transport spin on flags other ranks raise: every rank must own its GPU (two ranks sharing a
+   * device could wait on each other without ever being co-scheduled) */
+  {
+    char busid[B200_MAX_RANKS + 1][32], *db = NULL;
+    memset(busid, 0, sizeof(busid));
+    B200_CUDA(cudaDeviceGetPCIBusId(busid[0], 32, c.device));
+    B200_CUDA(cudaMalloc((void **)&db, 32 * (size_t)(c.size + 1)));
+    B200_CUDA(cudaMemcpy(db, busid[0], 32, cudaMemcpyHostToDevice));
+    B200_NCCL(g_nccl.AllGather(db, db + 32, 32, ncclChar, (ncclComm_t)c.nccl, c.stream));
+    B200_CUDA(cudaStreamSynchronize(c.stream));
+    B200_CUDA(cudaMemcpy(busid[1], db + 32, 32 * (size_t)c.size, cudaMemcpyDeviceToHost));
+    cudaFree(db);
+    for (int a = 0; a < c.size; a++)
+      for (int b = a + 1; b < c.size; b++)
+        if (!strncmp(busid[1 + a], busid[1 + b], 32)) {
+          cudaFree(P->arena); free(P);
+          return b200_seterr(B200_ERR_SUP, "ranks %d and %d share GPU %s: the peer-memory transport needs one GPU per rank (use the NCCL transport)", a, b, busid[1 + a]);
+        }
+  }
   for (int r = 0; r < c.size; r++) {
     if (r == c.rank) { P->peer[r] = P->arena; continue; }
     cudaError_t ce = cudaIpcOpenMemHandle((void **)&P->peer[r], all[r], cudaIpcMemLazyEnablePeerAccess);
