@@ -150,6 +150,11 @@ int b200_mat_bin_info2(b200_mat A, int *lanes_per_row, int *long_thresh, int *gr
  * (1, 2, 4, ... 32; 1 = every tile row is summed left to right exactly like aij.h:384-386), long-row threshold,
  * and whether products are parked in shared memory before the row sums (the choice for irregular row lengths). */
 int b200_spmv_set_tuning(int shape, int lanes_per_row, int long_thresh, int park);
+/* Column strips (cache blocking of the x gathers) for matrices created AFTER the call: -1 = automatic (strips of ~24 MB
+ * of x when x exceeds 48 MB and the mean row spans more than a strip), 0/1 = off, k = force k strips.  With one lane
+ * per row the row sums remain one left-to-right chain (bit-identical to MatMult_SeqAIJ). */
+int b200_spmv_set_strips(int nstrips);
+int b200_mat_strips(b200_mat A, int *diag_strips, int *offdiag_strips);
 /* the four fused entry points the CG driver uses (kept public so a KSP plugin can call them) */
 int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double *xdoty_host);   /* y = A x and x.y in one pass (seq, m == n)      */
 
@@ -190,6 +195,7 @@ int b200_mat_create_mpiaij(int m, int n_local, int N,
                            int nto, const int *to_procs, const int *to_starts, const int *to_indices,
                            int nfrom, const int *from_procs, const int *from_starts,
                            b200_mat *A);
+int b200_mat_mult_phases(b200_mat A, const double *x, double *y, double *ms4_host);  /* diagnostic: device ms of exchange-begin | diagonal | exchange-end | off-diagonal */
 int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost);         /* Mat_MPIAIJ::lvec, mpiaij.h:60   */
 int b200_mat_mpiaij_scatter(b200_mat A, const double *x);                     /* VecScatterBegin+End only        */
 int b200_mat_mpiaij_set_lvec(b200_mat A, const double *ghost_values_dev);     /* caller-performed scatter (P virtual ranks in one process) */

@@ -287,6 +287,11 @@ class Mat:
         _chk(lib.b200_mat_get_size(self.h, None, None, C.byref(nz)), "MatGetInfo")
         return nz.value
 
+    def strips(self):
+        a, b = C.c_int(), C.c_int()
+        _chk(lib.b200_mat_strips(self.h, C.byref(a), C.byref(b)), "strips")
+        return a.value, b.value
+
     def bin_info(self):
         a, b, c = C.c_int(), C.c_int(), C.c_int()
         _chk(lib.b200_mat_bin_info(self.h, C.byref(a), C.byref(b), C.byref(c)), "bin_info")
@@ -300,6 +305,11 @@ def spmv_tuning(shape=-1, lanes_per_row=-1, long_thresh=-1, park=-1):
     """Row-binning policy for matrices created after the call (-1 = automatic); lanes_per_row=1 makes every tile row
     a left-to-right sum, bit-identical to MatMult_SeqAIJ."""
     _chk(lib.b200_spmv_set_tuning(int(shape), int(lanes_per_row), int(long_thresh), int(park)), "spmv_tuning")
+
+
+def spmv_strips(nstrips=-1):
+    """Column strips for matrices created after the call: -1 automatic, 0 off, k forced (cache blocking of x)."""
+    _chk(lib.b200_spmv_set_strips(int(nstrips)), "spmv_strips")
 
 
 def ksp_options(**kw):

@@ -302,13 +302,19 @@ __global__ void __launch_bounds__(256) pack_put_kernel(int nsend, const int *__r
     while (i >= s_starts[k + 1]) k++;
     s_dst[k][i - s_starts[k]] = __ldg(&x[__ldg(&idx[i])]);
   }
-  __threadfence_system();
+  /* completion: CTA barrier, then ONE system-scope fence per CTA (cumulative over the CTA's stores through the barrier,
+   * the cooperative-groups grid-sync pattern) — a fence in every thread serialised 65 k MEMBAR.SYS and cost 15 us */
   __syncthreads();
-  if (tid == 0) s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  if (tid == 0) {
+    __threadfence_system();
+    s_last = (atomicAdd(ticket, 1u) == gridDim.x - 1);
+  }
   __syncthreads();
   if (!s_last) return;
-  __threadfence_system();
-  if (tid < plan.nto) st_release_sys(plan.rflag[tid], epoch);
+  if (tid < plan.nto) {
+    __threadfence_system();
+    st_release_sys(plan.rflag[tid], epoch);
+  }
   if (tid == 0) *ticket = 0;
 }
 
@@ -494,7 +500,7 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x)
   double *lvec = A->d_lvec[A->epoch & 1];
   if (A->peerplan) {
     PeerPlan *pp = (PeerPlan *)A->peerplan;
-    int g = (nsend + 255) / 256; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
+    int g = (nsend + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
     pack_put_kernel<<<g, 256, 0, c.stream>>>(nsend, A->d_to_indices, x, pp->dev, (int)(A->epoch & 1), (unsigned long long)A->epoch, pp->d_ticket);
     B200_LAUNCHED(1);
     return 0;

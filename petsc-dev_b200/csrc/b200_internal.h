@@ -77,6 +77,13 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
   int       *d_longstart;     /* [nlong+1] first chunk slot of each long row                                          */
   double    *d_longpart;      /* [nchunks] per-chunk partial sums                                                     */
   double    *d_dotpart;       /* [grid + nlong] per-CTA partials of the fused x.y                                    */
+  /* column strips (cache blocking for matrices whose x gathers would not stay in L2): when nstrips > 1 the block is
+   * stored as nstrips CSR blocks over disjoint column ranges (global column ids kept) and the product is
+   * y = S_0 x; y += S_1 x; ...  — for one lane per row the row sum is still one left-to-right chain */
+  int        nstrips;
+  B200Seq   *strips;
+  int        perm_pad;
+  long long *strip_nzoff;     /* unused on device; host: first entry of each strip in strip-major order (nstrips+1)  */
 };
 
 struct b200_mat_s {
@@ -100,6 +107,7 @@ int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
 int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);
+void b200_seq_dotparts(const B200Seq *S, const double **p, int *n);
 int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out);
 
 /* internal cross-file entry points */

@@ -196,10 +196,30 @@ __global__ void cg_begin_kernel(CgState *s) { if (threadIdx.x == 0 && s->reason 
 /* after p.w is known (cg.c:207-220) */
 struct CgAr { unsigned long long seq; unsigned long long *const *inbox; int rank, size; };   /* size <= 1: no allreduce */
 
-__global__ void __launch_bounds__(64) cg_after_dot_kernel(CgState *s, const CgAr ar)
+struct CgParts { const double *a; int na; const double *b; int nb; };   /* per-CTA partials of p.w left by the SpMV kernels */
+
+__global__ void __launch_bounds__(256) cg_after_dot_kernel(CgState *s, const CgAr ar, const CgParts parts)
 {
+  if (parts.na + parts.nb > 0) {
+    /* final, fixed-order reduction of the fused p.w partials (was a kernel of its own) */
+    __shared__ double s_w[8];
+    double t = 0.0;
+    for (int i = threadIdx.x; i < parts.na; i += 256) t += parts.a[i];
+    for (int i = threadIdx.x; i < parts.nb; i += 256) t += parts.b[i];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double u = 0.0;
+#pragma unroll
+      for (int q = 0; q < 8; q++) u += s_w[q];
+      s->red[3] = u;
+    }
+  }
   /* the allreduce is unconditional (collective): every rank runs the same number of them whatever s->reason says */
   if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[3], 1, 0, ar.seq, ar.rank, ar.size, ar.inbox);
+  else __syncthreads();
   if (threadIdx.x != 0 || s->reason != 0) return;
   s->dpi = s->red[3];
   s->betaold = s->beta;
@@ -208,11 +228,22 @@ __global__ void __launch_bounds__(64) cg_after_dot_kernel(CgState *s, const CgAr
   s->a = s->beta / s->dpi;
 }
 
-/* after the update kernel's reductions (cg.c:227-281): norm, history, KSPDefaultConverged, new beta, next top */
-__global__ void __launch_bounds__(64) cg_after_update_kernel(CgState *s, double *hist, const CgAr ar)
+__global__ void __launch_bounds__(256) cg_parts_kernel(CgState *s, const CgParts parts)   /* NCCL transport: local p.w only */
 {
-  if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[0], 3, 0, ar.seq, ar.rank, ar.size, ar.inbox);
-  if (threadIdx.x != 0 || s->reason != 0) return;
+  __shared__ double s_w[8];
+  double t = 0.0;
+  for (int i = threadIdx.x; i < parts.na; i += 256) t += parts.a[i];
+  for (int i = threadIdx.x; i < parts.nb; i += 256) t += parts.b[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = t;
+  __syncthreads();
+  if (threadIdx.x == 0) { double u = 0.0; for (int q = 0; q < 8; q++) u += s_w[q]; s->red[3] = u; }
+}
+
+/* after the update kernel's reductions (cg.c:227-281): norm, history, KSPDefaultConverged, new beta, next top */
+__device__ void cg_after_update_body(CgState *s, double *hist)   /* one thread; s->reason == 0 on entry */
+{
   double dp, beta = s->beta;
   if (s->normtype == B200_KSP_NORM_PRECONDITIONED) dp = sqrt(s->red[0]);
   else if (s->normtype == B200_KSP_NORM_UNPRECONDITIONED) dp = sqrt(s->red[2]);
@@ -237,6 +268,13 @@ __global__ void __launch_bounds__(64) cg_after_update_kernel(CgState *s, double 
   s->i++;
   if (s->i >= s->max_it) { s->reason = B200_KSP_DIVERGED_ITS; return; }
   cg_top(s);
+}
+
+__global__ void __launch_bounds__(64) cg_after_update_kernel(CgState *s, double *hist, const CgAr ar)
+{
+  if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[0], 3, 0, ar.seq, ar.rank, ar.size, ar.inbox);
+  if (threadIdx.x != 0 || s->reason != 0) return;
+  cg_after_update_body(s, hist);
 }
 
 /* p = z + b p  (VecCopy at i == 0, VecAYPX after: cg.c:194,202; b == 0 cannot occur for i > 0 unless beta == 0,
@@ -270,10 +308,10 @@ __global__ void __launch_bounds__(256) cg_pupdate_kernel(int n, const CgState *_
 }
 
 /* x += a p ; r -= a w ; z = r .* d (or z = r) ; partial sums of z.z, z.r, r.r  — 5 reads + 3 writes per row */
-template <bool JACOBI>
+template <bool JACOBI, bool INLINE_AFTER>
 __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, double *__restrict__ x, const double *__restrict__ p,
                                                         double *__restrict__ r, const double *__restrict__ w, double *__restrict__ z,
-                                                        const double *__restrict__ d, double *partials, unsigned *ticket)
+                                                        const double *__restrict__ d, double *partials, unsigned *ticket, double *hist)
 {
   if (s->reason != 0) return;
   const double a = s->a, ma = -a;
@@ -346,7 +384,12 @@ __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, doubl
       if (lane == 0) s->red[q] = u;
     }
   }
-  if (threadIdx.x == 0) *ticket = 0;
+  if (threadIdx.x == 0) {
+    *ticket = 0;
+    /* single rank: the scalar recurrences that follow (norm, convergence test, new beta) need no allreduce and run here,
+     * in the last CTA, instead of in a kernel of their own (thread 0 wrote red[] itself) */
+    if (INLINE_AFTER) cg_after_update_body(s, hist);
+  }
 }
 
 /* generic dot into a device scalar (MPIAIJ operator: p.w cannot ride on the two-part product) */
@@ -441,9 +484,9 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
   cg_begin_kernel<<<1, 32, 0, st>>>(ds);
   B200_LAUNCHED(1);
 
-  const bool seq = (A->kind == 0) && !A->A.compressed && (A->A.m == A->A.n);
+  const bool seq = (A->kind == 0) && !A->A.compressed && (A->A.m == A->A.n) && A->A.nstrips <= 1;
   const bool multi = c.size > 1;
-  const bool mpi_dot = (A->kind == 1) && !A->A.compressed && (A->A.m == A->A.n) && A->A.m > 0;
+  const bool mpi_dot = (A->kind == 1) && !A->A.compressed && (A->A.m == A->A.n) && A->A.m > 0 && A->A.nstrips <= 1 && A->B.nstrips <= 1;
   int gp = ((n + 1) / 2 + 255) / 256; if (gp > B200_NSM * 16) gp = B200_NSM * 16; if (gp < 1) gp = 1;
   const int gu = b200_red_grid((n + 1) / 2, 512, 2);
   if (check_every < 1) check_every = 1;
@@ -455,29 +498,45 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
       cg_pupdate_kernel<<<gp, 256, 0, st>>>(n, ds, P, Z);
       B200_LAUNCHED(1);
       CgAr ar1 = {0, NULL, c.rank, 1}, ar2 = {0, NULL, c.rank, 1};
-      if (seq) { rc = b200_seq_mult(&A->A, P, NULL, W, false, &ds->red[3]); if (rc) goto done; }
-      else if (mpi_dot) { rc = b200_mpiaij_mult_dot(A, P, W, &ds->red[3]); if (rc) goto done; }
-      else {
+      CgParts parts = {NULL, 0, NULL, 0};
+      if (seq) {
+        rc = b200_seq_mult_ex(&A->A, P, NULL, W, false, true, P, NULL); if (rc) goto done;
+        b200_seq_dotparts(&A->A, &parts.a, &parts.na);
+      } else if (mpi_dot) {
+        rc = b200_mpiaij_mult_dot(A, P, W, NULL); if (rc) goto done;
+        b200_seq_dotparts(&A->A, &parts.a, &parts.na);
+        b200_seq_dotparts(&A->B, &parts.b, &parts.nb);
+      } else {
         rc = op_mult(A, P, W); if (rc) goto done;
         cg_dot_kernel<<<b200_red_grid(n, 512, 4), 512, 0, st>>>(n, ds, P, W, c.d_partials, c.d_ticket, &ds->red[3]);
         B200_LAUNCHED(1);
       }
-      /* allreduce of p.w: folded into the scalar kernel over peer memory, else NCCL */
+      /* p.w: final reduction of the SpMV partials + allreduce (peer memory) + the scalar step, one kernel */
       if (multi) {
         if (b200_p2p_next(&ar1.seq, &ar1.inbox)) ar1.size = c.size;
-        else { rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done; }
+        else {
+          if (parts.na + parts.nb > 0) {          /* NCCL needs the local sum in memory first */
+            cg_parts_kernel<<<1, 256, 0, st>>>(ds, parts); B200_LAUNCHED(1);
+            parts.na = parts.nb = 0;
+          }
+          rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done;
+        }
       }
-      cg_after_dot_kernel<<<1, 64, 0, st>>>(ds, ar1);
-      B200_LAUNCHED(1);
-      if (pc->type == 1) cg_update_kernel<true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket);
-      else               cg_update_kernel<false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket);
+      cg_after_dot_kernel<<<1, 256, 0, st>>>(ds, ar1, parts);
       B200_LAUNCHED(1);
       if (multi) {
+        if (pc->type == 1) cg_update_kernel<true, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist);
+        else               cg_update_kernel<false, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist);
+        B200_LAUNCHED(1);
         if (b200_p2p_next(&ar2.seq, &ar2.inbox)) ar2.size = c.size;
         else { rc = b200_comm_allreduce_dev(&ds->red[0], 3, 0); if (rc) goto done; }
+        cg_after_update_kernel<<<1, 64, 0, st>>>(ds, dhist, ar2);
+        B200_LAUNCHED(1);
+      } else {
+        if (pc->type == 1) cg_update_kernel<true, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist);
+        else               cg_update_kernel<false, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist);
+        B200_LAUNCHED(1);
       }
-      cg_after_update_kernel<<<1, 64, 0, st>>>(ds, dhist, ar2);
-      B200_LAUNCHED(1);
     }
     launched += batch;
     if (cudaMemcpyAsync(ps, ds, sizeof(CgState), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {

@@ -64,11 +64,11 @@ __global__ void zero_rows_kernel(int n, double *y)
 }
 
 /* d[i] = a_ii or 0 (MatGetDiagonal_SeqAIJ aij.c:1040-1073); columns ascending -> bisection */
-__global__ void diag_kernel(int m, const int *__restrict__ ai, const int *__restrict__ aj, const double *__restrict__ aa,
+__global__ void diag_kernel(int r0, int m, const int *__restrict__ ai, const int *__restrict__ aj, const double *__restrict__ aa,
                             int coloff, double *__restrict__ d)
 {
   const int stride = gridDim.x * blockDim.x;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+  for (int i = r0 + blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
     int lo = ai[i], hi = ai[i + 1];
     const int want = i + coloff;
     double v = 0.0;
@@ -86,13 +86,17 @@ __global__ void diag_kernel(int m, const int *__restrict__ ai, const int *__rest
 void b200_seq_free(B200Seq *S)
 {
   if (!S) return;
+  if (S->strips) {
+    for (int k = 0; k < S->nstrips; k++) b200_seq_free(&S->strips[k]);
+    free(S->strips); free(S->strip_nzoff);
+  }
   if (S->d_ci && S->d_ci != S->d_i) cudaFree(S->d_ci);
   cudaFree(S->d_i); cudaFree(S->d_j); cudaFree(S->d_a); cudaFree(S->d_rindex);
   cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
   memset(S, 0, sizeof(*S));
 }
 
-int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a)
+static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a)
 {
   memset(S, 0, sizeof(*S));
   if (m < 0 || n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative matrix size %d x %d", m, n);
@@ -213,6 +217,82 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
   return 0;
 }
 
+static int g_tune_strips = -1;         /* -1 automatic, 0/1 off, k > 1 forced */
+
+/* How many column strips?  Stencil-like matrices gather from a narrow window of x that lives in L2 by itself; a matrix
+ * whose rows span (almost) all columns drags the whole of x through L2 against the matrix stream, and once x is larger
+ * than about half of the 126 MB L2 every gather goes to DRAM (measured: 10 M-row power-law matrix, x = 80 MB: 9.7 ms
+ * per product unblocked).  Strips of ~24 MB of x keep the active window resident. */
+static int choose_strips(int m, int n, const int *i, const int *j)
+{
+  int forced = g_tune_strips;
+  const char *e = getenv("B200_SPMV_STRIPS");
+  if (e) forced = atoi(e);
+  if (forced >= 0) return forced < 1 ? 1 : (forced > 64 ? 64 : forced);
+  if (8.0 * (double)n <= 48e6 || m == 0) return 1;
+  double span = 0.0; long long rows = 0;
+  const int step = m > (1 << 20) ? m >> 20 : 1;          /* sample about a million rows */
+  for (int r = 0; r < m; r += step) if (i[r + 1] > i[r]) { span += (double)(j[i[r + 1] - 1] - j[i[r]]); rows++; }
+  if (!rows || 8.0 * span / (double)rows <= 24e6) return 1;
+  int S = (int)((8.0 * (double)n + 24e6 - 1) / 24e6);
+  return S > 64 ? 64 : S;
+}
+
+int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a)
+{
+  memset(S, 0, sizeof(*S));
+  if (m < 0 || n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative matrix size %d x %d", m, n);
+  if (!i || i[0] != 0) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets must start at 0");
+  const long long nz = i[m];
+  const int ns = (nz > 0 && j) ? choose_strips(m, n, i, j) : 1;
+  if (ns <= 1) return seq_upload_one(S, m, n, i, j, a);
+  /* split by column range; within a row the entries of a strip are a contiguous run because columns ascend */
+  S->m = m; S->n = n; S->nz = nz; S->nstrips = ns;
+  S->strips = (B200Seq *)calloc((size_t)ns, sizeof(B200Seq));
+  S->strip_nzoff = (long long *)calloc((size_t)ns + 1, sizeof(long long));
+  if (!S->strips || !S->strip_nzoff) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  const int width = (int)(((long long)n + ns - 1) / ns);
+  int nonempty = 0;
+  for (int r = 0; r < m; r++) {
+    if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
+    nonempty += (i[r + 1] > i[r]);
+  }
+  S->nonzerorow = nonempty;
+  std::vector<int> si((size_t)m + 1), sj;
+  std::vector<double> sa;
+  std::vector<int> cur(i, i + m);                         /* next unread entry of every row */
+  for (int k = 0; k < ns; k++) {
+    const long long chi = (long long)(k + 1) * width;
+    sj.clear(); sa.clear();
+    si[0] = 0;
+    for (int r = 0; r < m; r++) {
+      int c = cur[r];
+      const int e = i[r + 1];
+      const int b = c;
+      while (c < e && (long long)j[c] < chi) c++;
+      sj.insert(sj.end(), j + b, j + c);
+      sa.insert(sa.end(), a + b, a + c);
+      cur[r] = c;
+      si[r + 1] = (int)sj.size();
+    }
+    S->strip_nzoff[k + 1] = S->strip_nzoff[k] + (long long)sj.size();
+    int rc = seq_upload_one(&S->strips[k], m, n, si.data(), sj.data(), sa.data());
+    if (rc) return rc;
+  }
+  /* the descriptive fields report the first strip's binning */
+  S->cfg = S->strips[0].cfg; S->G = S->strips[0].G; S->park = S->strips[0].park; S->long_thresh = S->strips[0].long_thresh;
+  S->grid = S->strips[0].grid;
+  for (int k = 0; k < ns; k++) { S->ntiles += S->strips[k].ntiles; S->nlong += S->strips[k].nlong; }
+  S->ncrows = m;
+  return 0;
+}
+
+extern "C" int b200_spmv_set_strips(int nstrips)
+{
+  g_tune_strips = nstrips;
+  return 0;
+}
+
 /* ---- tile-kernel dispatch: (launch shape) x (lanes per row) x (add, dot) */
 template <int G, bool PARK, int THREADS, int TILE_NNZ, int STAGES>
 static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
@@ -270,6 +350,14 @@ int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doubl
 {
   cudaStream_t st = g_b200.stream;
   if (S->m == 0) return 0;
+  if (S->nstrips > 1) {
+    if (want_dot) return b200_seterr(B200_ERR_SUP, "fused dot is not available for a column-stripped block");
+    for (int k = 0; k < S->nstrips; k++) {
+      /* the first strip starts the row sums (from 0 or from yin), every later one continues them in place */
+      B200_CHK(b200_seq_mult_ex(&S->strips[k], x, k == 0 ? yin : z, z, k == 0 ? add : true, false, NULL, NULL));
+    }
+    return 0;
+  }
   if (!dotx) dotx = x;
   if (add && z != yin && S->compressed) {
     /* rows the compressed list skips keep y (aij.c:1313-1315) */
@@ -300,6 +388,13 @@ int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doubl
   return 0;
 }
 
+/* where the last want_dot product left its per-CTA partials */
+void b200_seq_dotparts(const B200Seq *S, const double **p, int *n)
+{
+  *n = (S->m == 0) ? 0 : (S->ntiles ? S->grid : 0) + S->nlong;
+  *p = S->ntiles ? S->d_dotpart : S->d_dotpart + S->grid;
+}
+
 int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out)
 {
   return b200_seq_mult_ex(S, x, yin, z, add, dot_out != NULL, NULL, dot_out);
@@ -310,12 +405,12 @@ int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *
 int b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out)
 {
   const B200Seq *Sa = &A->A, *Sb = &A->B;
-  if (Sa->compressed || Sa->m != Sa->n) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square, uncompressed diagonal block");
+  if (Sa->compressed || Sa->m != Sa->n || Sa->nstrips > 1 || Sb->nstrips > 1) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square, uncompressed, unstripped diagonal block");
   B200_CHK(b200_mpiaij_exchange_begin(A, x));
   B200_CHK(b200_seq_mult_ex(Sa, x, NULL, y, false, true, x, NULL));
   B200_CHK(b200_mpiaij_exchange_end(A));
   B200_CHK(b200_seq_mult_ex(Sb, A->d_lvec[A->epoch & 1], y, y, true, true, x, NULL));
-  if (Sa->m == 0) return 0;
+  if (Sa->m == 0 || !dot_out) return 0;                          /* dot_out NULL: the caller reduces the partial lists itself */
   const int na = (Sa->ntiles ? Sa->grid : 0) + Sa->nlong, nb = (Sb->ntiles ? Sb->grid : 0) + Sb->nlong;
   dot_final_kernel<<<1, 1024, 0, g_b200.stream>>>(na, Sa->ntiles ? Sa->d_dotpart : Sa->d_dotpart + Sa->grid,
                                                   nb, Sb->ntiles ? Sb->d_dotpart : Sb->d_dotpart + Sb->grid, dot_out);
@@ -343,6 +438,7 @@ extern "C" int b200_mat_update_values(b200_mat A, const double *a)
   B200_NEED_INIT();
   if (!A || !a) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   if (A->kind != 0) return b200_seterr(B200_ERR_SUP, "value refresh is implemented for the sequential type");
+  if (A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "value refresh is not implemented for a column-stripped matrix (recreate it)");
   B200_CUDA(cudaMemcpyAsync(A->A.d_a, a, sizeof(double) * (size_t)A->A.nz, cudaMemcpyHostToDevice, g_b200.stream));
   B200_CUDA(cudaStreamSynchronize(g_b200.stream));
   return 0;
@@ -422,6 +518,31 @@ extern "C" int b200_mat_mult(b200_mat A, const double *x, double *y)
   return b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], y, y, true, NULL);
 }
 
+/* diagnostic: one MPIAIJ MatMult with CUDA events between its phases (exchange begin | diagonal block | exchange end |
+ * off-diagonal block); each phase includes the launch gap in front of it */
+extern "C" int b200_mat_mult_phases(b200_mat A, const double *x, double *y, double *ms4)
+{
+  B200_NEED_INIT();
+  if (!A || !x || !y || !ms4) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
+  static cudaEvent_t ev[5];
+  static bool made = false;
+  if (!made) { for (int k = 0; k < 5; k++) B200_CUDA(cudaEventCreate(&ev[k])); made = true; }
+  cudaStream_t st = g_b200.stream;
+  B200_CUDA(cudaEventRecord(ev[0], st));
+  B200_CHK(b200_mpiaij_exchange_begin(A, x));
+  B200_CUDA(cudaEventRecord(ev[1], st));
+  B200_CHK(b200_seq_mult(&A->A, x, NULL, y, false, NULL));
+  B200_CUDA(cudaEventRecord(ev[2], st));
+  B200_CHK(b200_mpiaij_exchange_end(A));
+  B200_CUDA(cudaEventRecord(ev[3], st));
+  B200_CHK(b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], y, y, true, NULL));
+  B200_CUDA(cudaEventRecord(ev[4], st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  for (int k = 0; k < 4; k++) { float f = 0; B200_CUDA(cudaEventElapsedTime(&f, ev[k], ev[k + 1])); ms4[k] = f; }
+  return 0;
+}
+
 extern "C" int b200_mat_multadd(b200_mat A, const double *x, const double *y, double *z)
 {
   B200_NEED_INIT();
@@ -439,7 +560,7 @@ extern "C" int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double 
 {
   B200_NEED_INIT();
   if (!A || !x || !y || !xdoty) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
-  if (A->kind != 0 || A->A.m != A->A.n || A->A.compressed) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square sequential matrix");
+  if (A->kind != 0 || A->A.m != A->A.n || A->A.compressed || A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square sequential matrix stored as one block");
   B200_CHK(b200_seq_mult(&A->A, x, NULL, y, false, g_b200.d_res));
   return b200_reduce_finish(1, xdoty, false, 0);
 }
@@ -452,9 +573,31 @@ extern "C" int b200_mat_get_diagonal(b200_mat A, double *d)
   if (S->m == 0) return 0;
   /* the diagonal block stores local column ids, so the diagonal entry of local row i is column i in both types
    * (MatGetDiagonal_MPIAIJ forwards to the diagonal block, mpiaij.c:1246-1256) */
+  if (S->nstrips > 1) {
+    /* the diagonal entry of row i sits in the strip that owns column i */
+    const int width = (int)(((long long)S->n + S->nstrips - 1) / S->nstrips);
+    B200_CUDA(cudaMemsetAsync(d, 0, sizeof(double) * (size_t)S->m, g_b200.stream));
+    for (int k = 0; k < S->nstrips; k++) {
+      const int r0 = k * width, r1 = (k + 1) * width < S->m ? (k + 1) * width : S->m;
+      if (r0 >= r1) continue;
+      const B200Seq *C = &S->strips[k];
+      int g = (r1 - r0 + 255) / 256; if (g > B200_NSM * 8) g = B200_NSM * 8;
+      diag_kernel<<<g, 256, 0, g_b200.stream>>>(r0, r1, C->d_i, C->d_j, C->d_a, 0, d);
+      B200_LAUNCHED(1);
+    }
+    return 0;
+  }
   int g = (S->m + 255) / 256; if (g > B200_NSM * 8) g = B200_NSM * 8;
-  diag_kernel<<<g, 256, 0, g_b200.stream>>>(S->m, S->d_i, S->d_j, S->d_a, 0, d);
+  diag_kernel<<<g, 256, 0, g_b200.stream>>>(0, S->m, S->d_i, S->d_j, S->d_a, 0, d);
   B200_LAUNCHED(1);
+  return 0;
+}
+
+extern "C" int b200_mat_strips(b200_mat A, int *diag_strips, int *offdiag_strips)
+{
+  if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null matrix");
+  if (diag_strips) *diag_strips = A->A.nstrips > 1 ? A->A.nstrips : 1;
+  if (offdiag_strips) *offdiag_strips = A->kind ? (A->B.nstrips > 1 ? A->B.nstrips : 1) : 0;
   return 0;
 }
 

@@ -329,6 +329,27 @@ static PetscErrorCode MatDestroy_MPIAIJB200(Mat A)                              
   PetscFunctionReturn(0);
 }
 
+/* the device operator behind a seqaijb200 / mpiaijb200 matrix (uploaded or refreshed first), for the KSP types */
+#undef __FUNCT__
+#define __FUNCT__ "MatB200GetHandle"
+PetscErrorCode MatB200GetHandle(Mat A,void **handle)
+{
+  PetscBool      isseq,ismpi;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = PetscObjectTypeCompare((PetscObject)A,MATSEQAIJB200,&isseq);CHKERRQ(ierr);
+  ierr = PetscObjectTypeCompare((PetscObject)A,MATMPIAIJB200,&ismpi);CHKERRQ(ierr);
+  if (isseq) {
+    ierr = MatB200CopyToDevice_SeqAIJ(A);CHKERRQ(ierr);
+    *handle = (void*)((Mat_SeqAIJB200*)A->spptr)->mat;
+  } else if (ismpi) {
+    ierr = MatB200CopyToDevice_MPIAIJ(A);CHKERRQ(ierr);
+    *handle = (void*)((Mat_MPIAIJB200*)((Mat_MPIAIJ*)A->data)->spptr)->mat;
+  } else SETERRQ1(((PetscObject)A)->comm,PETSC_ERR_SUP,"Matrix of type %s where a B200 matrix (aijb200) is needed",((PetscObject)A)->type_name);
+  PetscFunctionReturn(0);
+}
+
 EXTERN_C_BEGIN
 #undef __FUNCT__
 #define __FUNCT__ "MatCreate_MPIAIJB200"

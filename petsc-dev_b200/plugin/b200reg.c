@@ -60,6 +60,9 @@ PetscErrorCode PetscB200Register(void)
   ierr = MatRegisterBaseName(MATAIJB200,MATSEQAIJB200,MATMPIAIJB200);CHKERRQ(ierr);
   ierr = MatRegister(MATSEQAIJB200,0,"MatCreate_SeqAIJB200",MatCreate_SeqAIJB200);CHKERRQ(ierr);
   ierr = MatRegister(MATMPIAIJB200,0,"MatCreate_MPIAIJB200",MatCreate_MPIAIJB200);CHKERRQ(ierr);
+  /* device-resident Krylov drivers as NEW KSP types (itregis.c:69 registers the reference's the same way) */
+  ierr = KSPRegister(KSPCGB200,0,"KSPCreate_CGB200",KSPCreate_CGB200);CHKERRQ(ierr);
+  ierr = KSPRegister(KSPGMRESB200,0,"KSPCreate_GMRESB200",KSPCreate_GMRESB200);CHKERRQ(ierr);
   ierr = PetscRegisterFinalize(PetscB200Finalize);CHKERRQ(ierr);
   PetscB200Registered = PETSC_TRUE;
   PetscFunctionReturn(0);

@@ -48,7 +48,7 @@ def main(verbose=True):
         raise SystemExit("build oracle/_ref/libpetsc_ref.so first (oracle/build_ref.py)")
     os.makedirs(LIBDIR, exist_ok=True)
     os.makedirs(BINDIR, exist_ok=True)
-    srcs = [os.path.join(HERE, f) for f in ("b200vec.c", "b200mat.c", "b200reg.c")]
+    srcs = [os.path.join(HERE, f) for f in ("b200vec.c", "b200mat.c", "b200ksp.c", "b200reg.c")]
     deps = srcs + [os.path.join(HERE, "petscb200plugin.h"), os.path.join(ROOT, "include", "petscb200.h"),
                    os.path.join(CONF, "petscconf.h")]
     if newer(PLUGIN, deps):

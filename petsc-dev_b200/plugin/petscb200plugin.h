@@ -19,6 +19,7 @@
 
 #include <petscmat.h>
 #include <petscvec.h>
+#include <petscksp.h>
 
 #define VECSEQB200    "seqb200"
 #define VECMPIB200    "mpib200"
@@ -26,6 +27,8 @@
 #define MATSEQAIJB200 "seqaijb200"
 #define MATMPIAIJB200 "mpiaijb200"
 #define MATAIJB200    "aijb200"
+#define KSPCGB200     "cgb200"
+#define KSPGMRESB200  "gmresb200"
 
 EXTERN_C_BEGIN
 extern PetscErrorCode PetscB200Register(void);
@@ -35,6 +38,8 @@ extern PetscErrorCode VecCreate_MPIB200(Vec);
 extern PetscErrorCode VecCreate_B200(Vec);
 extern PetscErrorCode MatCreate_SeqAIJB200(Mat);
 extern PetscErrorCode MatCreate_MPIAIJB200(Mat);
+extern PetscErrorCode KSPCreate_CGB200(KSP);
+extern PetscErrorCode KSPCreate_GMRESB200(KSP);
 EXTERN_C_END
 
 /* where the newest copy of a vector lives (the role of PetscCUSPFlag, include/petscsys.h) */
@@ -45,6 +50,7 @@ extern PetscErrorCode VecB200GetDeviceRead(Vec, const PetscScalar **);
 extern PetscErrorCode VecB200GetDeviceWrite(Vec, PetscScalar **);      /* contents undefined, caller overwrites all of it */
 extern PetscErrorCode VecB200GetDeviceReadWrite(Vec, PetscScalar **);
 extern PetscErrorCode VecB200GetWhere(Vec, B200VecWhere *);
+extern PetscErrorCode MatB200GetHandle(Mat, void **b200_mat_handle);   /* device operator of an aijb200 matrix, refreshed */
 /* counters for tests: host<->device copies the coherence protocol performed, device matrix uploads */
 extern PetscErrorCode PetscB200GetCounters(PetscInt *h2d, PetscInt *d2h, PetscInt *matuploads, PetscInt *matvalueupdates);
 

@@ -25,6 +25,16 @@ CASES = {
                               b200_args=B200, history=True),
     "ksp_ex2_mpiaij": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "30", "-n", "30", "-ksp_type", "cg", "-pc_type", "jacobi"],
                            ref_args=["-mat_type", "mpiaij", "-vec_type", "mpi"], b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"], history=True),
+    # the device-resident Krylov drivers as new KSP types (-ksp_type cgb200 / gmresb200) against the reference's KSPCG / KSPGMRES
+    "ksp_ex2_cgb200": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "40", "-n", "37", "-pc_type", "jacobi"],
+                           ref_args=["-ksp_type", "cg"], b200_args=B200 + ["-ksp_type", "cgb200"], history=True),
+    "ksp_ex2_cgb200_opbyop": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "31", "-n", "29", "-pc_type", "jacobi", "-random_exact_sol"],
+                                  ref_args=["-ksp_type", "cg"], b200_args=B200 + ["-ksp_type", "cgb200", "-ksp_b200_fused", "0"], history=True),
+    "ksp_ex2_cgb200_mpiaij": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "30", "-n", "30", "-pc_type", "none"],
+                                  ref_args=["-ksp_type", "cg", "-mat_type", "mpiaij", "-vec_type", "mpi"],
+                                  b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200", "-ksp_type", "cgb200"], history=True),
+    "ksp_ex2_gmresb200": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "33", "-n", "41", "-pc_type", "jacobi", "-ksp_gmres_restart", "30"],
+                              ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
     # src/mat/examples/tests/makefile:753,774,795
     "mat_ex5_11_A": dict(prog="mat_ex5", args=["-rectA"], ref_args=["-mat_type", "seqaij"], b200_args=["-mat_type", "seqaijb200", "-vec_type", "seqb200"],
                          golden="src/mat/examples/tests/output/ex5_11_A.out"),
