@@ -141,6 +141,10 @@ int b200_mat_destroy(b200_mat A);
 int b200_mat_get_size(b200_mat A, int *m, int *n, long long *nz);
 int b200_mat_mult(b200_mat A, const double *x, double *y);                    /* MatMult_SeqAIJ aij.c:1225 / MatMult_MPIAIJ mpiaij.c:1102       */
 int b200_mat_multadd(b200_mat A, const double *x, const double *y, double *z); /* MatMultAdd_SeqAIJ aij.c:1291 / _MPIAIJ mpiaij.c:1132 ; z may alias y */
+/* Transposed products.  The explicit transpose is built once at the first call (rows = source rows ascending), so every
+ * y[j] receives its terms in the order MatMultTranspose_SeqAIJ adds them (aij.c:1108-1118) and the product streams. */
+int b200_mat_multtranspose(b200_mat A, const double *x, double *y);                     /* MatMultTranspose_SeqAIJ aij.c:1127 / _MPIAIJ mpiaij.c:1147 */
+int b200_mat_multtransposeadd(b200_mat A, const double *x, const double *y, double *z); /* MatMultTransposeAdd_SeqAIJ aij.c:1078 / _MPIAIJ mpiaij.c:1178 ; z may alias y */
 int b200_mat_get_diagonal(b200_mat A, double *d);                             /* MatGetDiagonal_SeqAIJ aij.c:1040 / _MPIAIJ mpiaij.c:1246       */
 int b200_mat_flops(b200_mat A, double *mult_flops);                           /* 2*nz - nonzerorow, aij.c:1281                                 */
 int b200_mat_bytes(b200_mat A, double *mult_bytes);                           /* algorithmic bytes of one MatMult                  */

@@ -95,3 +95,32 @@ def mult(R, ranges, S, x, add_y=None):
             yr = B.multadd(lvec, yr, inplace=True)
         y[rs:re_] = yr
     return y
+
+
+def mult_transpose(R, ranges, S, x, add_y=None):
+    """MatMultTranspose_MPIAIJ / MatMultTransposeAdd_MPIAIJ (mpiaij.c:1147-1195) over all virtual ranks with the reference's
+    sequential kernels: lvec_r = B_r^T x_r, y_r = A_r^T x_r (+ y_r), then the reverse scatter with ADD_VALUES; the messages
+    an owner receives are added in ascending source-rank order (the reference adds them in arrival order)."""
+    size = len(S)
+    y = np.empty(int(ranges[-1]))
+    lv = []
+    for r in range(size):
+        s = S[r]
+        rs, re_ = int(ranges[r]), int(ranges[r + 1])
+        m = s["m"]
+        A = R.RefMat(m, m, s["Ai"], s["Aj"], s["Aa"], no_inode=True)
+        y[rs:re_] = A.multtranspose(x[rs:re_], None if add_y is None else add_y[rs:re_])
+        if s["garray"].size:
+            B = R.RefMat(m, s["garray"].size, s["Bi"], s["Bj"], s["Ba"], no_inode=True)
+            lv.append(B.multtranspose(x[rs:re_]))
+        else:
+            lv.append(np.zeros(0))
+    for p in range(size):
+        ps, pe = int(ranges[p]), int(ranges[p + 1])
+        for r in range(size):
+            if r == p or not S[r]["garray"].size:
+                continue
+            g = S[r]["garray"]
+            sel = (g >= ps) & (g < pe)
+            y[g[sel]] = y[g[sel]] + lv[r][sel]
+    return y

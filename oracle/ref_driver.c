@@ -138,6 +138,28 @@ int ref_mat_multadd(void *h, int kind, const double *x, double *y, double *z)
   return 0;
 }
 
+/* y = A^T x (MatMultTranspose) ; with yin != NULL z = yin + A^T x (MatMultTransposeAdd), z may alias yin */
+int ref_mat_multtranspose(void *h, int kind, const double *x, double *yin, double *z)
+{
+  Mat            A = (Mat)h;
+  Vec            xv, yv = 0, zv;
+  PetscErrorCode ierr;
+  PetscInt       m, n;
+  ierr = MatGetLocalSize(A, &m, &n); REFCHK(ierr);
+  ierr = wrapvec(A, kind, m, x, &xv); REFCHK(ierr);
+  ierr = wrapvec(A, kind, n, z, &zv); REFCHK(ierr);
+  if (!yin) { ierr = MatMultTranspose(A, xv, zv); REFCHK(ierr); }
+  else {
+    if (yin == z) yv = zv;
+    else { ierr = wrapvec(A, kind, n, yin, &yv); REFCHK(ierr); }
+    ierr = MatMultTransposeAdd(A, xv, yv, zv); REFCHK(ierr);
+    if (yv != zv) { ierr = VecDestroy(&yv); REFCHK(ierr); }
+  }
+  ierr = VecDestroy(&xv); REFCHK(ierr);
+  ierr = VecDestroy(&zv); REFCHK(ierr);
+  return 0;
+}
+
 int ref_mat_get_diagonal(void *h, int kind, double *d)
 {
   Mat            A = (Mat)h;

@@ -116,6 +116,14 @@ class RefMat:
         _chk(lib().ref_mat_multadd(self.h, self.kind, _dp(x), _dp(y), _dp(z)), "MatMultAdd")
         return z
 
+    def multtranspose(self, x, y=None):
+        """A^T x (MatMultTranspose) or y + A^T x (MatMultTransposeAdd)."""
+        x = _f64(x)
+        z = np.empty(self.n, np.float64)
+        yy = _f64(y).copy() if y is not None else None
+        _chk(lib().ref_mat_multtranspose(self.h, self.kind, _dp(x), _dp(yy) if yy is not None else None, _dp(z)), "MatMultTranspose")
+        return z
+
     def diagonal(self):
         d = np.empty(self.m, np.float64)
         _chk(lib().ref_mat_get_diagonal(self.h, self.kind, _dp(d)), "MatGetDiagonal")

@@ -264,6 +264,12 @@ class Mat:
     def mult_add(self, x, y, z):            # MatMultAdd(A, x, y, z)
         _chk(lib.b200_mat_multadd(self.h, x.p, y.p, z.p), "MatMultAdd")
 
+    def mult_transpose(self, x, y):         # MatMultTranspose(A, x, y)
+        _chk(lib.b200_mat_multtranspose(self.h, x.p, y.p), "MatMultTranspose")
+
+    def mult_transpose_add(self, x, y, z):  # MatMultTransposeAdd(A, x, y, z)
+        _chk(lib.b200_mat_multtransposeadd(self.h, x.p, y.p, z.p), "MatMultTransposeAdd")
+
     def mult_dot(self, x, y):
         r = C.c_double()
         _chk(lib.b200_mat_mult_dot(self.h, x.p, y.p, C.byref(r)), "MatMult+VecDot")

@@ -271,8 +271,12 @@ struct PeerPlanDev {
   const unsigned long long *const *lflag;        /* [nfrom] local arrival flag written by sender k                   */
 };
 struct PeerPlan {
-  PeerPlanDev dev;
+  PeerPlanDev dev;                               /* forward: x -> neighbours' ghost vectors (MatMult)                */
+  PeerPlanDev rev;                               /* reverse: my ghost contributions -> their owners (MatMultTranspose) */
   void       *d_blob;                            /* one device allocation behind the tables above                    */
+  void       *d_blob_rev;
+  double     *rbuf[2];                           /* arena: what the neighbours return to me (nsend entries, by parity) */
+  unsigned   *d_ticket_rev;
   size_t      arena_lo, arena_hi;                /* arena range owned by this matrix                                 */
   unsigned   *d_ticket;
 };
@@ -300,7 +304,7 @@ __global__ void __launch_bounds__(256) pack_put_kernel(int nsend, const int *__r
   int k = 0;
   for (int i = blockIdx.x * blockDim.x + tid; i < nsend; i += stride) {
     while (i >= s_starts[k + 1]) k++;
-    s_dst[k][i - s_starts[k]] = __ldg(&x[__ldg(&idx[i])]);
+    s_dst[k][i - s_starts[k]] = __ldg(&x[idx ? __ldg(&idx[i]) : i]);
   }
   /* completion: CTA barrier, then ONE system-scope fence per CTA (cumulative over the CTA's stores through the barrier,
    * the cooperative-groups grid-sync pattern) — a fence in every thread serialised 65 k MEMBAR.SYS and cost 15 us */
@@ -329,7 +333,7 @@ static void peerplan_free(b200_mat M)
   PeerPlan *pp = (PeerPlan *)M->peerplan;
   if (!pp) return;
   B200P2P *P = g_b200.peer;
-  cudaFree(pp->d_blob); cudaFree(pp->d_ticket);
+  cudaFree(pp->d_blob); cudaFree(pp->d_ticket); cudaFree(pp->d_blob_rev); cudaFree(pp->d_ticket_rev);
   if (P && P->bump == pp->arena_hi) P->bump = pp->arena_lo;      /* last one in: give the arena range back          */
   free(pp);
   M->peerplan = NULL;
@@ -337,25 +341,59 @@ static void peerplan_free(b200_mat M)
 }
 void b200_mpiaij_peer_free(b200_mat M) { peerplan_free(M); }
 
-/* collective: carve the ghost vectors / flags / credits out of the arena and learn where every neighbour put theirs */
+/* device tables of one direction: starts[ns+1] | dst[2*ns] | rflag[ns] | lcredit[ns] | rcredit[nr] | lflag[nr] */
+static int plan_blob(PeerPlanDev *dev, void **d_blob, int ns, const int *starts, void *const *dst0, void *const *dst1,
+                     void *const *rflag, void *const *lcredit, int nr, void *const *rcredit, void *const *lflag)
+{
+  const size_t n_int = (size_t)((ns + 1 + 1) & ~1);
+  const size_t nptr = (size_t)(4 * ns + 2 * nr);
+  const size_t bytes = n_int * sizeof(int) + nptr * sizeof(void *) + 16;
+  char *hb = (char *)calloc(1, bytes);
+  if (!hb) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  int *h_starts = (int *)hb;
+  void **hp = (void **)(hb + n_int * sizeof(int));
+  for (int k = 0; k <= ns; k++) h_starts[k] = starts[k];
+  for (int k = 0; k < ns; k++) { hp[k] = dst0[k]; hp[ns + k] = dst1[k]; hp[2 * ns + k] = rflag[k]; hp[3 * ns + k] = lcredit[k]; }
+  for (int k = 0; k < nr; k++) { hp[4 * ns + k] = rcredit[k]; hp[4 * ns + nr + k] = lflag[k]; }
+  B200_CUDA(cudaMalloc(d_blob, bytes));
+  B200_CUDA(cudaMemcpy(*d_blob, hb, bytes, cudaMemcpyHostToDevice));
+  free(hb);
+  char *db = (char *)*d_blob;
+  void **dp = (void **)(db + n_int * sizeof(int));
+  dev->nto = ns; dev->nfrom = nr;
+  dev->to_starts = (const int *)db;
+  dev->dst     = (double *const *)(dp);
+  dev->rflag   = (unsigned long long *const *)(dp + 2 * ns);
+  dev->lcredit = (const unsigned long long *const *)(dp + 3 * ns);
+  dev->rcredit = (unsigned long long *const *)(dp + 4 * ns);
+  dev->lflag   = (const unsigned long long *const *)(dp + 4 * ns + nr);
+  return 0;
+}
+
+/* collective: carve the ghost vectors / return buffers / flags / credits out of the arena and learn where every
+ * neighbour put theirs */
 static int peerplan_build(b200_mat M)
 {
   B200Ctx &c = g_b200;
   B200P2P *P = c.peer;
-  const int size = c.size, rank = c.rank, nghost = M->nghost;
-  /* meta[r] = { ok, off_lvec0, off_lvec1, off_flag, off_credit, recv_start[0..size) } */
-  const int W = 5 + B200_MAX_RANKS;
-  long long mine[5 + B200_MAX_RANKS], all[B200_MAX_RANKS][5 + B200_MAX_RANKS];
+  const int size = c.size, rank = c.rank, nghost = M->nghost, R = B200_MAX_RANKS;
+  const int nto = M->nto, nfrom = M->nfrom, nsend = M->to_starts[nto];
+  /* meta = { ok, lvec0, lvec1, flag, credit, rbuf0, rbuf1, rflag, rcredit, recv_start[R], send_start[R] } */
+  enum { OK = 0, LV0, LV1, FLG, CRD, RB0, RB1, RFLG, RCRD, RECV0 };
+  const int W = RECV0 + 2 * B200_MAX_RANKS;
+  long long mine[RECV0 + 2 * B200_MAX_RANKS], all[B200_MAX_RANKS][RECV0 + 2 * B200_MAX_RANKS];
   const size_t lo = P->bump;
-  size_t o0 = 0, o1 = 0, of = 0, oc = 0;
-  int fail = p2p_alloc(sizeof(double) * (size_t)(nghost + 2), &o0);
-  if (!fail) fail = p2p_alloc(sizeof(double) * (size_t)(nghost + 2), &o1);
-  if (!fail) fail = p2p_alloc(sizeof(unsigned long long) * B200_MAX_RANKS, &of);
-  if (!fail) fail = p2p_alloc(sizeof(unsigned long long) * B200_MAX_RANKS, &oc);
+  size_t off[RECV0] = {0};
+  const size_t want[RECV0] = {0, sizeof(double) * (size_t)(nghost + 2), sizeof(double) * (size_t)(nghost + 2), 8 * (size_t)R, 8 * (size_t)R,
+                              sizeof(double) * (size_t)(nsend + 2), sizeof(double) * (size_t)(nsend + 2), 8 * (size_t)R, 8 * (size_t)R};
+  int fail = 0;
+  for (int k = 1; k < RECV0 && !fail; k++) fail = p2p_alloc(want[k], &off[k]);
   const size_t hi = P->bump;
-  mine[0] = fail ? 0 : 1; mine[1] = (long long)o0; mine[2] = (long long)o1; mine[3] = (long long)of; mine[4] = (long long)oc;
-  for (int r = 0; r < B200_MAX_RANKS; r++) mine[5 + r] = -1;
-  for (int k = 0; k < M->nfrom; k++) mine[5 + M->from_procs[k]] = M->from_starts[k];
+  mine[OK] = fail ? 0 : 1;
+  for (int k = 1; k < RECV0; k++) mine[k] = (long long)off[k];
+  for (int r = 0; r < 2 * R; r++) mine[RECV0 + r] = -1;
+  for (int k = 0; k < nfrom; k++) mine[RECV0 + M->from_procs[k]] = M->from_starts[k];
+  for (int k = 0; k < nto; k++)   mine[RECV0 + R + M->to_procs[k]] = M->to_starts[k];
   long long *dm = NULL;
   B200_CUDA(cudaMalloc((void **)&dm, sizeof(long long) * (size_t)W * (size_t)(size + 1)));
   B200_CUDA(cudaMemcpy(dm, mine, sizeof(mine), cudaMemcpyHostToDevice));
@@ -364,57 +402,55 @@ static int peerplan_build(b200_mat M)
   B200_CUDA(cudaMemcpy(all, dm + W, sizeof(long long) * (size_t)W * (size_t)size, cudaMemcpyDeviceToHost));
   cudaFree(dm);
   bool ok = true;
-  for (int r = 0; r < size; r++) ok = ok && all[r][0] == 1;
+  for (int r = 0; r < size; r++) ok = ok && all[r][OK] == 1;
   if (!ok) { P->bump = lo; return 1; }                            /* every rank sees the same table -> same decision  */
-  for (int k = 0; k < M->nto; k++)
-    if (all[M->to_procs[k]][5 + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not expect the entries rank %d sends", M->to_procs[k], rank);
-  if (!fail) {
-    B200_CUDA(cudaMemsetAsync(P->arena + o0, 0, sizeof(double) * (size_t)(nghost + 2), c.stream));
-    B200_CUDA(cudaMemsetAsync(P->arena + o1, 0, sizeof(double) * (size_t)(nghost + 2), c.stream));
-    B200_CUDA(cudaMemsetAsync(P->arena + of, 0, sizeof(unsigned long long) * B200_MAX_RANKS, c.stream));
-    B200_CUDA(cudaMemsetAsync(P->arena + oc, 0, sizeof(unsigned long long) * B200_MAX_RANKS, c.stream));
-  }
+  for (int k = 0; k < nto; k++)
+    if (all[M->to_procs[k]][RECV0 + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not expect the entries rank %d sends", M->to_procs[k], rank);
+  for (int k = 0; k < nfrom; k++)
+    if (all[M->from_procs[k]][RECV0 + R + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not send to rank %d what it expects", M->from_procs[k], rank);
+  for (int k = 1; k < RECV0; k++) B200_CUDA(cudaMemsetAsync(P->arena + off[k], 0, want[k], c.stream));
   PeerPlan *pp = (PeerPlan *)calloc(1, sizeof(PeerPlan));
   if (!pp) return b200_seterr(B200_ERR_MEM, "out of host memory");
   pp->arena_lo = lo; pp->arena_hi = hi;
-  const int nto = M->nto, nfrom = M->nfrom;
-  /* blob layout: to_starts[nto+1] ints (padded to 8 B) | dst[2*nto] | rflag[nto] | lcredit[nto] | rcredit[nfrom] | lflag[nfrom] */
-  const size_t n_int = (size_t)((nto + 1 + 1) & ~1);
-  const size_t nptr = (size_t)(4 * nto + 2 * nfrom);
-  const size_t bytes = n_int * sizeof(int) + nptr * sizeof(void *) + 16;
-  char *hb = (char *)calloc(1, bytes);
-  int *h_starts = (int *)hb;
-  void **hp = (void **)(hb + n_int * sizeof(int));
-  for (int k = 0; k <= nto; k++) h_starts[k] = M->to_starts[k];
+  void *d0[B200_MAX_RANKS] = {0}, *d1[B200_MAX_RANKS] = {0}, *rf[B200_MAX_RANKS] = {0}, *lc[B200_MAX_RANKS] = {0}, *rc[B200_MAX_RANKS] = {0}, *lf[B200_MAX_RANKS] = {0};
+  /* forward: I send to to_procs (their ghost vectors), I receive from from_procs */
   for (int k = 0; k < nto; k++) {
     const int q = M->to_procs[k];
-    const long long rs = all[q][5 + rank];
-    hp[0 * nto + k] = P->peer[q] + all[q][1] + 8 * rs;                                  /* dst parity 0 */
-    hp[1 * nto + k] = P->peer[q] + all[q][2] + 8 * rs;                                  /* dst parity 1 */
-    hp[2 * nto + k] = P->peer[q] + all[q][3] + 8 * (size_t)rank;                        /* rflag        */
-    hp[3 * nto + k] = P->arena + oc + 8 * (size_t)q;                                    /* lcredit      */
+    const long long rs = all[q][RECV0 + rank];
+    d0[k] = P->peer[q] + all[q][LV0] + 8 * rs;
+    d1[k] = P->peer[q] + all[q][LV1] + 8 * rs;
+    rf[k] = P->peer[q] + all[q][FLG] + 8 * (size_t)rank;
+    lc[k] = P->arena + off[CRD] + 8 * (size_t)q;
   }
   for (int k = 0; k < nfrom; k++) {
     const int q = M->from_procs[k];
-    hp[4 * nto + k]         = P->peer[q] + all[q][4] + 8 * (size_t)rank;                /* rcredit      */
-    hp[4 * nto + nfrom + k] = P->arena + of + 8 * (size_t)q;                            /* lflag        */
+    rc[k] = P->peer[q] + all[q][CRD] + 8 * (size_t)rank;
+    lf[k] = P->arena + off[FLG] + 8 * (size_t)q;
   }
-  B200_CUDA(cudaMalloc(&pp->d_blob, bytes));
-  B200_CUDA(cudaMemcpy(pp->d_blob, hb, bytes, cudaMemcpyHostToDevice));
-  free(hb);
+  B200_CHK(plan_blob(&pp->dev, &pp->d_blob, nto, M->to_starts, d0, d1, rf, lc, nfrom, rc, lf));
+  /* reverse: I send my ghost contributions to from_procs (their return buffers), I receive from to_procs */
+  for (int k = 0; k < nfrom; k++) {
+    const int q = M->from_procs[k];
+    const long long ss = all[q][RECV0 + R + rank];
+    d0[k] = P->peer[q] + all[q][RB0] + 8 * ss;
+    d1[k] = P->peer[q] + all[q][RB1] + 8 * ss;
+    rf[k] = P->peer[q] + all[q][RFLG] + 8 * (size_t)rank;
+    lc[k] = P->arena + off[RCRD] + 8 * (size_t)q;
+  }
+  for (int k = 0; k < nto; k++) {
+    const int q = M->to_procs[k];
+    rc[k] = P->peer[q] + all[q][RCRD] + 8 * (size_t)rank;
+    lf[k] = P->arena + off[RFLG] + 8 * (size_t)q;
+  }
+  B200_CHK(plan_blob(&pp->rev, &pp->d_blob_rev, nfrom, M->from_starts, d0, d1, rf, lc, nto, rc, lf));
   B200_CUDA(cudaMalloc((void **)&pp->d_ticket, sizeof(unsigned)));
   B200_CUDA(cudaMemset(pp->d_ticket, 0, sizeof(unsigned)));
-  char *db = (char *)pp->d_blob;
-  void **dp = (void **)(db + n_int * sizeof(int));
-  pp->dev.nto = nto; pp->dev.nfrom = nfrom;
-  pp->dev.to_starts = (const int *)db;
-  pp->dev.dst     = (double *const *)(dp);
-  pp->dev.rflag   = (unsigned long long *const *)(dp + 2 * nto);
-  pp->dev.lcredit = (const unsigned long long *const *)(dp + 3 * nto);
-  pp->dev.rcredit = (unsigned long long *const *)(dp + 4 * nto);
-  pp->dev.lflag   = (const unsigned long long *const *)(dp + 4 * nto + nfrom);
-  M->d_lvec[0] = (double *)(P->arena + o0);
-  M->d_lvec[1] = (double *)(P->arena + o1);
+  B200_CUDA(cudaMalloc((void **)&pp->d_ticket_rev, sizeof(unsigned)));
+  B200_CUDA(cudaMemset(pp->d_ticket_rev, 0, sizeof(unsigned)));
+  M->d_lvec[0] = (double *)(P->arena + off[LV0]);
+  M->d_lvec[1] = (double *)(P->arena + off[LV1]);
+  pp->rbuf[0] = (double *)(P->arena + off[RB0]);
+  pp->rbuf[1] = (double *)(P->arena + off[RB1]);
   M->peerplan = pp;
   /* the zeroing above must be complete on every rank before anybody's first store can land */
   B200_CUDA(cudaStreamSynchronize(c.stream));
@@ -544,4 +580,74 @@ extern "C" int b200_mat_mpiaij_scatter(b200_mat A, const double *x)
   if (!A || A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
   B200_CHK(b200_mpiaij_exchange_begin(A, x));
   return b200_mpiaij_exchange_end(A);
+}
+
+/* ------------------------------------------------------------------------------------------------ reverse exchange */
+/* UnPack_1 with ADD_VALUES (vpscat.c:520-570) for ONE neighbour's message: y[indices[i]] += buf[i].  The messages are
+ * applied neighbour by neighbour in ascending rank order (the reference applies them in MPI_Waitany arrival order), so
+ * entries that several neighbours contribute to are summed in a fixed order. */
+__global__ void __launch_bounds__(256) unpack_add_kernel(int n, const int *__restrict__ idx, const double *__restrict__ buf, double *y)
+{
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) { const int r = __ldg(&idx[i]); y[r] = y[r] + buf[i]; }
+}
+
+/* MatMultTranspose_MPIAIJ / MatMultTransposeAdd_MPIAIJ (mpiaij.c:1147-1195): lvec = B^T x ; reverse scatter (ADD) begins ;
+ * z = A^T x (+ y) ; scatter ends: every rank adds what its neighbours computed for the rows it owns. */
+int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, double *z)
+{
+  B200Ctx &c = g_b200;
+  if (!A || A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
+  B200_CHK(b200_seq_transpose(&A->A));
+  B200_CHK(b200_seq_transpose(&A->B));
+  const int nghost = A->nghost, nto = A->nto, nfrom = A->nfrom;
+  const bool exchange = c.size > 1 && (nto || nfrom);
+  if (!A->d_ghost_t) {
+    B200_CUDA(cudaMalloc((void **)&A->d_ghost_t, sizeof(double) * (size_t)(nghost + 2)));
+    B200_CUDA(cudaMemset(A->d_ghost_t, 0, sizeof(double) * (size_t)(nghost + 2)));
+  }
+  if (nghost) { B200_CHK(b200_seq_mult(A->B.T, x, NULL, A->d_ghost_t, false, NULL)); }
+  const double *buf = A->d_sendbuf;
+  A->repoch++;
+  if (exchange) {
+    if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "MPIAIJ MatMultTranspose on %d ranks needs b200_comm_init", c.size);
+    if (A->peerplan) {
+      PeerPlan *pp = (PeerPlan *)A->peerplan;
+      int g = (nghost + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
+      pack_put_kernel<<<g, 256, 0, c.stream>>>(nghost, NULL, A->d_ghost_t, pp->rev, (int)(A->repoch & 1), (unsigned long long)A->repoch, pp->d_ticket_rev);
+      B200_LAUNCHED(1);
+      buf = pp->rbuf[A->repoch & 1];
+    } else {
+      B200_CUDA(cudaEventRecord(c.ev_fork, c.stream));
+      B200_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork, 0));
+      B200_NCCL(g_nccl.GroupStart());
+      for (int k = 0; k < nto; k++)
+        B200_NCCL(g_nccl.Recv(A->d_sendbuf + A->to_starts[k], (size_t)(A->to_starts[k + 1] - A->to_starts[k]), ncclDouble, A->to_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
+      for (int k = 0; k < nfrom; k++)
+        B200_NCCL(g_nccl.Send(A->d_ghost_t + A->from_starts[k], (size_t)(A->from_starts[k + 1] - A->from_starts[k]), ncclDouble, A->from_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
+      B200_NCCL(g_nccl.GroupEnd());
+      B200_CUDA(cudaEventRecord(c.ev_join, c.comm_stream));
+    }
+  }
+  /* local part */
+  if (A->A.m == 0) { if (yin && z != yin && A->A.n > 0) B200_CHK(b200_vec_copy(A->A.n, yin, z)); }
+  else if (yin) { B200_CHK(b200_seq_mult(A->A.T, x, yin, z, true, NULL)); }
+  else { B200_CHK(b200_seq_mult(A->A.T, x, NULL, z, false, NULL)); }
+  if (!exchange) return 0;
+  if (A->peerplan) {
+    if (nto) {
+      wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->rev, (unsigned long long)A->repoch);
+      B200_LAUNCHED(1);
+    }
+  } else {
+    B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+  }
+  for (int k = 0; k < nto; k++) {
+    const int len = A->to_starts[k + 1] - A->to_starts[k];
+    if (len <= 0) continue;
+    int g = (len + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
+    unpack_add_kernel<<<g, 256, 0, c.stream>>>(len, A->d_to_indices + A->to_starts[k], buf + A->to_starts[k], z);
+    B200_LAUNCHED(1);
+  }
+  return 0;
 }

@@ -82,6 +82,8 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
    * y = S_0 x; y += S_1 x; ...  — for one lane per row the row sum is still one left-to-right chain */
   int        nstrips;
   B200Seq   *strips;
+  int        req_G;           /* lanes-per-row request in force when the block was created (-1 automatic)            */
+  B200Seq   *T;               /* explicit transpose (n x m CSR, source rows ascending), built at the first MatMultTranspose */
   int        perm_pad;
   long long *strip_nzoff;     /* unused on device; host: first entry of each strip in strip-major order (nstrips+1)  */
 };
@@ -100,6 +102,8 @@ struct b200_mat_s {
   int     *d_to_indices;      /* [to_starts[nto]] local offsets to pack                                               */
   double  *d_sendbuf;         /* packed send values                                                                   */
   long long epoch;            /* exchange counter                                                                     */
+  long long repoch;           /* reverse-exchange counter (MatMultTranspose)                                          */
+  double  *d_ghost_t;         /* [nghost] B^T x, what this rank contributes to rows its neighbours own                */
   void    *peerplan;          /* per-matrix peer-store plan (b200_comm.cu)                                            */
 };
 
@@ -107,6 +111,7 @@ int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
 int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);
+int  b200_seq_transpose(B200Seq *S);
 void b200_seq_dotparts(const B200Seq *S, const double **p, int *n);
 int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out);
 
@@ -115,6 +120,7 @@ int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_ma
 int b200_comm_allreduce_dev(double *dvals, int n, int op_max);
 int b200_mpiaij_exchange_begin(b200_mat A, const double *x);
 int b200_mpiaij_exchange_end(b200_mat A);
+int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, double *z);   /* yin NULL: plain transpose product */
 void b200_mpiaij_peer_free(b200_mat A);
 bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox);
 

@@ -86,6 +86,7 @@ __global__ void diag_kernel(int r0, int m, const int *__restrict__ ai, const int
 void b200_seq_free(B200Seq *S)
 {
   if (!S) return;
+  if (S->T) { b200_seq_free(S->T); free(S->T); S->T = NULL; }
   if (S->strips) {
     for (int k = 0; k < S->nstrips; k++) b200_seq_free(&S->strips[k]);
     free(S->strips); free(S->strip_nzoff);
@@ -104,7 +105,7 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   const long long nz = i[m];
   if (nz < 0) return b200_seterr(B200_ERR_ARG_WRONG, "negative nonzero count");
   if (nz > 0 && (!j || !a)) return b200_seterr(B200_ERR_ARG_NULL, "null column/value arrays");
-  S->m = m; S->n = n; S->nz = nz;
+  S->m = m; S->n = n; S->nz = nz; S->req_G = g_tune_G;
   /* row statistics + the visiting order */
   int nonempty = 0;
   for (int r = 0; r < m; r++) {
@@ -247,7 +248,7 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
   const int ns = (nz > 0 && j) ? choose_strips(m, n, i, j) : 1;
   if (ns <= 1) return seq_upload_one(S, m, n, i, j, a);
   /* split by column range; within a row the entries of a strip are a contiguous run because columns ascend */
-  S->m = m; S->n = n; S->nz = nz; S->nstrips = ns;
+  S->m = m; S->n = n; S->nz = nz; S->nstrips = ns; S->req_G = g_tune_G;
   S->strips = (B200Seq *)calloc((size_t)ns, sizeof(B200Seq));
   S->strip_nzoff = (long long *)calloc((size_t)ns + 1, sizeof(long long));
   if (!S->strips || !S->strip_nzoff) return b200_seterr(B200_ERR_MEM, "out of host memory");
@@ -291,6 +292,48 @@ extern "C" int b200_spmv_set_strips(int nstrips)
 {
   g_tune_strips = nstrips;
   return 0;
+}
+
+/* The explicit transpose, built once (lazily) from the device copy: MatMultTranspose_SeqAIJ (aij.c:1078-1135) walks
+ * the rows in order and does y[j] += x[i] a_ij, so every y[j] receives its terms in ascending source-row order; a CSR
+ * of A^T whose rows list the source rows ascending, multiplied by the one-lane-per-row kernel starting from y (or 0),
+ * performs exactly the same additions in the same order — bit-identical, and it streams like any other MatMult
+ * instead of scattering atomics. */
+int b200_seq_transpose(B200Seq *S)
+{
+  if (S->T) return 0;
+  const int m = S->m, n = S->n;
+  const int nblk = S->nstrips > 1 ? S->nstrips : 1;
+  std::vector<int> ti((size_t)n + 1, 0);
+  std::vector<std::vector<int>>    bi(nblk), bj(nblk);
+  std::vector<std::vector<double>> ba(nblk);
+  for (int k = 0; k < nblk; k++) {
+    const B200Seq *C = S->nstrips > 1 ? &S->strips[k] : S;
+    bi[k].resize((size_t)m + 1); bj[k].resize((size_t)C->nz); ba[k].resize((size_t)C->nz);
+    B200_CUDA(cudaMemcpy(bi[k].data(), C->d_i, sizeof(int) * ((size_t)m + 1), cudaMemcpyDeviceToHost));
+    if (C->nz) {
+      B200_CUDA(cudaMemcpy(bj[k].data(), C->d_j, sizeof(int) * (size_t)C->nz, cudaMemcpyDeviceToHost));
+      B200_CUDA(cudaMemcpy(ba[k].data(), C->d_a, sizeof(double) * (size_t)C->nz, cudaMemcpyDeviceToHost));
+    }
+    for (long long e = 0; e < C->nz; e++) ti[(size_t)bj[k][(size_t)e] + 1]++;
+  }
+  for (int c = 0; c < n; c++) ti[(size_t)c + 1] += ti[c];
+  std::vector<int> tj((size_t)S->nz), pos(ti.begin(), ti.end() - 1);
+  std::vector<double> ta((size_t)S->nz);
+  for (int k = 0; k < nblk; k++)                                  /* a column lives in exactly one strip */
+    for (int r = 0; r < m; r++)
+      for (int e = bi[k][r]; e < bi[k][(size_t)r + 1]; e++) {
+        const int c = bj[k][e], p = pos[c]++;
+        tj[p] = r; ta[p] = ba[k][e];
+      }
+  S->T = (B200Seq *)calloc(1, sizeof(B200Seq));
+  if (!S->T) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  const int keepG = g_tune_G;
+  g_tune_G = S->req_G;                                            /* the transpose follows its parent's lanes-per-row request */
+  int rc = b200_seq_upload(S->T, n, m, ti.data(), tj.data(), ta.data());
+  g_tune_G = keepG;
+  if (rc) { b200_seq_free(S->T); free(S->T); S->T = NULL; }
+  return rc;
 }
 
 /* ---- tile-kernel dispatch: (launch shape) x (lanes per row) x (add, dot) */
@@ -439,6 +482,7 @@ extern "C" int b200_mat_update_values(b200_mat A, const double *a)
   if (!A || !a) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   if (A->kind != 0) return b200_seterr(B200_ERR_SUP, "value refresh is implemented for the sequential type");
   if (A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "value refresh is not implemented for a column-stripped matrix (recreate it)");
+  if (A->A.T) { b200_seq_free(A->A.T); free(A->A.T); A->A.T = NULL; }        /* rebuilt from the new values on demand */
   B200_CUDA(cudaMemcpyAsync(A->A.d_a, a, sizeof(double) * (size_t)A->A.nz, cudaMemcpyHostToDevice, g_b200.stream));
   B200_CUDA(cudaStreamSynchronize(g_b200.stream));
   return 0;
@@ -556,6 +600,28 @@ extern "C" int b200_mat_multadd(b200_mat A, const double *x, const double *y, do
   return b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], z, z, true, NULL);
 }
 
+extern "C" int b200_mat_multtranspose(b200_mat A, const double *x, double *y)
+{
+  B200_NEED_INIT();
+  if (!A || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (x == y) return b200_seterr(B200_ERR_ARG_IDN, "x and y must be different vectors");   /* matrix.c:2207 */
+  if (A->kind != 0) return b200_mpiaij_multtranspose(A, x, NULL, y);
+  B200_CHK(b200_seq_transpose(&A->A));
+  if (A->A.n > 0 && A->A.m == 0) return b200_vec_set(A->A.n, y, 0.0);
+  return b200_seq_mult(A->A.T, x, NULL, y, false, NULL);
+}
+
+extern "C" int b200_mat_multtransposeadd(b200_mat A, const double *x, const double *y, double *z)
+{
+  B200_NEED_INIT();
+  if (!A || !x || !y || !z) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (x == z) return b200_seterr(B200_ERR_ARG_IDN, "x and z must be different vectors");
+  if (A->kind != 0) return b200_mpiaij_multtranspose(A, x, y, z);
+  B200_CHK(b200_seq_transpose(&A->A));
+  if (A->A.m == 0) return (z != y && A->A.n > 0) ? b200_vec_copy(A->A.n, y, z) : 0;
+  return b200_seq_mult(A->A.T, x, y, z, true, NULL);
+}
+
 extern "C" int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double *xdoty)
 {
   B200_NEED_INIT();
@@ -609,6 +675,7 @@ extern "C" int b200_mat_destroy(b200_mat A)
   if (A->kind) {
     b200_seq_free(&A->B);
     if (A->peerplan) b200_mpiaij_peer_free(A);
+    cudaFree(A->d_ghost_t);
     cudaFree(A->d_garray); cudaFree(A->d_lvec[0]); cudaFree(A->d_lvec[1]); cudaFree(A->d_to_indices); cudaFree(A->d_sendbuf);
     free(A->to_procs); free(A->to_starts); free(A->from_procs); free(A->from_starts);
   }

@@ -3,7 +3,7 @@
  * Mirrors MatCreate_SeqAIJCUSP (reference src/mat/impls/aij/seq/seqcusp/aijcusp.cu:657-681) and MatCreate_MPIAIJCUSP
  * (src/mat/impls/aij/mpi/mpicusp/mpiaijcusp.cu:192-226): inherit the complete host CSR type (MatCreate_SeqAIJ aij.c:3886,
  * MatCreate_MPIAIJ mpiaij.c:5617 — preallocation, MatSetValues, assembly, views, MatGetDiagonal ... all stay host code),
- * override mult / multadd / getvecs / destroy, switch the inode path off (aijcusp.cu:665).
+ * override mult / multadd / multtranspose / multtransposeadd / getvecs / destroy, switch the inode path off (aijcusp.cu:665).
  *
  * Device copy: built lazily at the first MatMult after the matrix changed.  "Changed" is detected with the object state
  * every mutating Mat front end bumps (MatAssemblyEnd, MatScale, MatShift, MatZeroEntries, MatDiagonalScale, MatZeroRows:
@@ -107,6 +107,46 @@ static PetscErrorCode MatMultAdd_SeqAIJB200(Mat A,Vec xx,Vec yy,Vec zz)         
 }
 
 #undef __FUNCT__
+#define __FUNCT__ "MatMultTranspose_SeqAIJB200"
+static PetscErrorCode MatMultTranspose_SeqAIJB200(Mat A,Vec xx,Vec yy)            /* MatMultTranspose_SeqAIJ aij.c:1127 */
+{
+  Mat_SeqAIJ        *a = (Mat_SeqAIJ*)A->data;
+  const PetscScalar *x;
+  PetscScalar       *y;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_SeqAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceWrite(yy,&y);CHKERRQ(ierr);
+  CHKB200(b200_mat_multtranspose(((Mat_SeqAIJB200*)A->spptr)->mat,x,y));
+  ierr = PetscLogFlops(2.0*a->nz);CHKERRQ(ierr);                                  /* aij.c:1120 */
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMultTransposeAdd_SeqAIJB200"
+static PetscErrorCode MatMultTransposeAdd_SeqAIJB200(Mat A,Vec xx,Vec yy,Vec zz)  /* MatMultTransposeAdd_SeqAIJ aij.c:1078 */
+{
+  Mat_SeqAIJ        *a = (Mat_SeqAIJ*)A->data;
+  const PetscScalar *x,*y;
+  PetscScalar       *z;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_SeqAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  if (zz == yy) { ierr = VecB200GetDeviceReadWrite(zz,&z);CHKERRQ(ierr); y = z; }
+  else {
+    ierr = VecB200GetDeviceRead(yy,&y);CHKERRQ(ierr);
+    ierr = VecB200GetDeviceWrite(zz,&z);CHKERRQ(ierr);
+  }
+  CHKB200(b200_mat_multtransposeadd(((Mat_SeqAIJB200*)A->spptr)->mat,x,y,z));
+  ierr = PetscLogFlops(2.0*a->nz);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
 #define __FUNCT__ "MatGetVecs_SeqAIJB200"
 static PetscErrorCode MatGetVecs_SeqAIJB200(Mat mat,Vec *right,Vec *left)         /* MatGetVecs_SeqAIJCUSP aijcusp.cu:324 */
 {
@@ -163,6 +203,8 @@ PetscErrorCode MatCreate_SeqAIJB200(Mat B)
   B->spptr        = (void*)d;
   B->ops->mult    = MatMult_SeqAIJB200;
   B->ops->multadd = MatMultAdd_SeqAIJB200;
+  B->ops->multtranspose    = MatMultTranspose_SeqAIJB200;
+  B->ops->multtransposeadd = MatMultTransposeAdd_SeqAIJB200;
   B->ops->getvecs = MatGetVecs_SeqAIJB200;
   B->ops->destroy = MatDestroy_SeqAIJB200;
   ierr = PetscObjectChangeTypeName((PetscObject)B,MATSEQAIJB200);CHKERRQ(ierr);
@@ -288,6 +330,49 @@ static PetscErrorCode MatMultAdd_MPIAIJB200(Mat A,Vec xx,Vec yy,Vec zz)         
 }
 
 #undef __FUNCT__
+#define __FUNCT__ "MatMultTranspose_MPIAIJB200"
+static PetscErrorCode MatMultTranspose_MPIAIJB200(Mat A,Vec xx,Vec yy)            /* MatMultTranspose_MPIAIJ mpiaij.c:1147 */
+{
+  Mat_MPIAIJ        *a = (Mat_MPIAIJ*)A->data;
+  Mat_SeqAIJ        *ad = (Mat_SeqAIJ*)a->A->data,*ao = (Mat_SeqAIJ*)a->B->data;
+  const PetscScalar *x;
+  PetscScalar       *y;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_MPIAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceWrite(yy,&y);CHKERRQ(ierr);
+  /* B^T x, reverse ghost exchange (ADD) GPU to GPU overlapped with A^T x: all inside the library */
+  CHKB200(b200_mat_multtranspose(((Mat_MPIAIJB200*)a->spptr)->mat,x,y));
+  ierr = PetscLogFlops(2.0*ad->nz + 2.0*ao->nz);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
+#define __FUNCT__ "MatMultTransposeAdd_MPIAIJB200"
+static PetscErrorCode MatMultTransposeAdd_MPIAIJB200(Mat A,Vec xx,Vec yy,Vec zz)  /* MatMultTransposeAdd_MPIAIJ mpiaij.c:1178 */
+{
+  Mat_MPIAIJ        *a = (Mat_MPIAIJ*)A->data;
+  Mat_SeqAIJ        *ad = (Mat_SeqAIJ*)a->A->data,*ao = (Mat_SeqAIJ*)a->B->data;
+  const PetscScalar *x,*y;
+  PetscScalar       *z;
+  PetscErrorCode    ierr;
+
+  PetscFunctionBegin;
+  ierr = MatB200CopyToDevice_MPIAIJ(A);CHKERRQ(ierr);
+  ierr = VecB200GetDeviceRead(xx,&x);CHKERRQ(ierr);
+  if (zz == yy) { ierr = VecB200GetDeviceReadWrite(zz,&z);CHKERRQ(ierr); y = z; }
+  else {
+    ierr = VecB200GetDeviceRead(yy,&y);CHKERRQ(ierr);
+    ierr = VecB200GetDeviceWrite(zz,&z);CHKERRQ(ierr);
+  }
+  CHKB200(b200_mat_multtransposeadd(((Mat_MPIAIJB200*)a->spptr)->mat,x,y,z));
+  ierr = PetscLogFlops(2.0*ad->nz + 2.0*ao->nz);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
+#undef __FUNCT__
 #define __FUNCT__ "MatGetVecs_MPIAIJB200"
 static PetscErrorCode MatGetVecs_MPIAIJB200(Mat mat,Vec *right,Vec *left)         /* MatGetVecs_MPIAIJCUSP mpiaijcusp.cu:59 */
 {
@@ -367,6 +452,8 @@ PetscErrorCode MatCreate_MPIAIJB200(Mat A)
   a->spptr        = (void*)d;
   A->ops->mult    = MatMult_MPIAIJB200;
   A->ops->multadd = MatMultAdd_MPIAIJB200;
+  A->ops->multtranspose    = MatMultTranspose_MPIAIJB200;
+  A->ops->multtransposeadd = MatMultTransposeAdd_MPIAIJB200;
   A->ops->getvecs = MatGetVecs_MPIAIJB200;
   A->ops->destroy = MatDestroy_MPIAIJB200;
   ierr = PetscObjectChangeTypeName((PetscObject)A,MATMPIAIJB200);CHKERRQ(ierr);

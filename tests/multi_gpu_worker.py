@@ -71,6 +71,11 @@ def main():
         got = gather(z)
         A.mult_add(x, y, z)
         got_add = gather(z)
+        for _ in range(3):                            # reverse exchange (ADD): repeated, both parities of the return buffers
+            A.mult_transpose(x, z)
+        got_t = gather(z)
+        A.mult_transpose_add(x, y, z)
+        got_tadd = gather(z)
         # vector reductions across ranks
         dot = x.dot(y)
         nrm = x.norm()
@@ -93,6 +98,15 @@ def main():
             want = O.mult(R, ranges, S, xh)
             want_add = O.mult(R, ranges, S, xh, add_y=yh)
             res = {}
+            want_t = O.mult_transpose(R, ranges, S, xh)
+            want_tadd = O.mult_transpose(R, ranges, S, xh, add_y=yh)
+            sct = np.maximum(np.abs(want_t), 1.0)
+            if name in ("plaw", "bs3"):               # several lanes per transposed row (bs3: 81 entries) -> tolerance
+                res["multtranspose_ok"] = bool(np.all(np.abs(got_t - want_t) <= 1e-12 * sct) and
+                                               np.all(np.abs(got_tadd - want_tadd) <= 1e-12 * (sct + np.abs(yh))))
+            else:
+                res["multtranspose_ok"] = bool(np.array_equal(got_t, want_t) and np.array_equal(got_tadd, want_tadd))
+            res["multtranspose_max_abs_err"] = float(np.max(np.abs(got_t - want_t)))
             if name == "plaw":
                 sc = np.maximum(np.abs(want), 1.0)
                 res["mult_ok"] = bool(np.all(np.abs(got - want) <= 1e-12 * sc))

@@ -244,3 +244,74 @@ def test_strips_automatic_choice(gpu, P):
     ip, j, a = P.laplace3d_7pt(16)
     A = gpu.Mat.from_csr(16 ** 3, 16 ** 3, ip, j, a)
     assert A.strips() == (1, 0)
+
+
+@pytest.mark.parametrize("name", ["ex5", "lap7", "s27", "rect", "plaw", "bs3"])
+def test_mult_transpose(gpu, R, P, name):
+    """MatMultTranspose / MatMultTransposeAdd against MatMultTranspose_SeqAIJ (aij.c:1078-1135): the explicit transpose lists
+    source rows ascending, so with one lane per row every y[j] receives its terms in the reference's order -> bit-exact;
+    several lanes per row (bs3, plaw) -> 1e-12 of the term magnitudes."""
+    lanes = 1
+    if name == "ex5":
+        m, n, ip, j, a = ex5_matrix()
+    elif name == "lap7":
+        m = n = 14 ** 3; ip, j, a = P.laplace3d_7pt(14)
+    elif name == "s27":
+        m = n = 10 ** 3; ip, j, a = P.stencil3d_27pt(10)
+    elif name == "rect":
+        ip, j, a = P.laplace2d_5pt(30, 40, 100, 700); ip = ip - ip[0]; m, n = 600, 1200
+    elif name == "plaw":
+        m = n = 3000; ip, j, a = P.powerlaw(3000, seed=4, xm=4.0, lmax=500); lanes = -1
+    else:
+        m = n = 3 * 6 ** 3; ip, j, a = P.elasticity_bs3(6); lanes = -1
+    gpu.spmv_tuning(lanes_per_row=lanes)
+    try:
+        A = gpu.Mat.from_csr(m, n, ip, j, a)
+    finally:
+        gpu.spmv_tuning()
+    ref = R.RefMat(m, n, ip, j, a, no_inode=True)
+    xh, yh = P.random_vector(m, 5), P.random_vector(n, 6)
+    x, y, z = gpu.Vec(m, xh), gpu.Vec(n, yh), gpu.Vec(n)
+    A.mult_transpose(x, z)
+    want = ref.multtranspose(xh)
+    cols = np.asarray(j)
+    rows = np.repeat(np.arange(m), np.diff(ip))
+    scale = np.bincount(cols, weights=np.abs(a * xh[rows]), minlength=n)
+    got = z.get_array()
+    if lanes == 1:
+        assert np.array_equal(got, want)
+    assert np.all(np.abs(got - want) <= 1e-12 * scale)
+    A.mult_transpose_add(x, y, z)
+    want2 = ref.multtranspose(xh, yh)
+    got = z.get_array()
+    if lanes == 1:
+        assert np.array_equal(got, want2)
+    assert np.all(np.abs(got - want2) <= 1e-12 * (scale + np.abs(yh)))
+    A.mult_transpose_add(x, y, y)                          # z aliases y
+    assert np.array_equal(y.get_array(), got)
+    # the forward product is untouched by the transpose's existence
+    u, v = gpu.Vec(n, yh), gpu.Vec(m)
+    A.mult(u, v)
+    if lanes == 1:
+        assert np.array_equal(v.get_array(), ref.mult(yh))
+
+
+def test_mult_transpose_strips_and_refresh(gpu, R, P):
+    """Transpose of a column-stripped matrix, and value refresh drops the cached transpose."""
+    m = n = 12 ** 3
+    ip, j, a = P.laplace3d_7pt(12)
+    gpu.spmv_strips(3); gpu.spmv_tuning(lanes_per_row=1)
+    try:
+        A = gpu.Mat.from_csr(m, n, ip, j, a)
+    finally:
+        gpu.spmv_strips(-1); gpu.spmv_tuning()
+    xh = P.random_vector(m, 7)
+    x, z = gpu.Vec(m, xh), gpu.Vec(n)
+    A.mult_transpose(x, z)
+    assert np.array_equal(z.get_array(), R.RefMat(m, n, ip, j, a, no_inode=True).multtranspose(xh))
+    B = gpu.Mat.from_csr(m, n, ip, j, a)
+    B.mult_transpose(x, z)
+    a2 = a * 1.5 + 0.25
+    B.update_values(a2)
+    B.mult_transpose(x, z)
+    assert np.array_equal(z.get_array(), R.RefMat(m, n, ip, j, a2, no_inode=True).multtranspose(xh))

@@ -45,6 +45,7 @@ def test_virtual_ranks(gpu, R, P, name, size, lanes):
         got_add[rs:re_] = z.get_array()
         if size > 1 and name != "plaw":
             assert A.nnz() == h["split"]["Aj"].size + h["split"]["Bj"].size
+        del A
     if name == "plaw" or (lanes != 1 and name in ("s27", "bs3")):
         sc = np.maximum(np.abs(want), 1.0)
         assert np.all(np.abs(got - want) <= 1e-12 * sc) and np.all(np.abs(got_add - want_add) <= 1e-12 * (sc + np.abs(yh)))
