@@ -204,6 +204,21 @@ int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost);         /*
 int b200_mat_mpiaij_scatter(b200_mat A, const double *x);                     /* VecScatterBegin+End only        */
 int b200_mat_mpiaij_set_lvec(b200_mat A, const double *ghost_values_dev);     /* caller-performed scatter (P virtual ranks in one process) */
 
+/* ---- device-resident VecScatter (parallel vector <-> sequential vector) ---------------------------------------------
+ * The general MPI -> Seq scatter of VecScatterCreate_PtoS (vpscat.c:1730-1924) with VecScatterBegin_1 / End_1
+ * (vpscat.h:14-233): built from the lists b200_scatter_plan_from/_to produce (block lists already expanded to scalar
+ * entries).  x is this rank's part of the parallel vector, y the sequential vector; add 0 = INSERT_VALUES, 1 = ADD_VALUES;
+ * reverse 0 = SCATTER_FORWARD (y[from_indices] <- x of the owners), 1 = SCATTER_REVERSE (x of the owners <- y).  Messages
+ * travel GPU to GPU (NVLink peer stores or NCCL); received messages are applied neighbour by neighbour in ascending rank
+ * order; the self part is applied in Begin (vpscat.h:100-128).  Collective. */
+int b200_scatter_create(int nx_local, int ny,
+                        int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                        int nfrom, const int *from_procs, const int *from_starts, const int *from_indices,
+                        int nlocal, const int *to_local, const int *from_local, b200_scatter *ctx);
+int b200_scatter_begin(b200_scatter ctx, double *x, double *y, int add, int reverse);
+int b200_scatter_end(b200_scatter ctx, double *x, double *y, int add, int reverse);
+int b200_scatter_destroy(b200_scatter ctx);
+
 /* ---- KSP drivers ----------------------------------------------------------------------------------------------
  * Restatements of KSPSolve_CG (src/ksp/ksp/impls/cg/cg.c:92-286) and KSPSolve_GMRES / KSPGMRESCycle
  * (src/ksp/ksp/impls/gmres/gmres.c:118-238, borthog2.c:35-118) with PCJACOBI / PCNONE

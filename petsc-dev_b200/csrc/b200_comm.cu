@@ -21,6 +21,8 @@
 #include "b200_internal.h"
 #include <dlfcn.h>
 #include <nccl.h>
+#include <vector>
+#include <algorithm>
 #include "b200_p2p_dev.cuh"
 
 struct NcclApi {
@@ -592,6 +594,52 @@ __global__ void __launch_bounds__(256) unpack_add_kernel(int n, const int *__res
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) { const int r = __ldg(&idx[i]); y[r] = y[r] + buf[i]; }
 }
 
+/* reverse exchange, first half: every rank's ghost-side values (nghost entries, grouped by owner like lvec) travel to
+ * their owners; *buf_out is where this rank will find what its neighbours returned (nsend entries, to_starts order) */
+static int reverse_begin(b200_mat A, const double *ghost_values, const double **buf_out)
+{
+  B200Ctx &c = g_b200;
+  const int nghost = A->nghost, nto = A->nto, nfrom = A->nfrom;
+  *buf_out = A->d_sendbuf;
+  A->repoch++;
+  if (c.size <= 1 || (nto == 0 && nfrom == 0)) return 0;
+  if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "a reverse ghost exchange on %d ranks needs b200_comm_init", c.size);
+  if (A->peerplan) {
+    PeerPlan *pp = (PeerPlan *)A->peerplan;
+    int g = (nghost + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
+    pack_put_kernel<<<g, 256, 0, c.stream>>>(nghost, NULL, ghost_values, pp->rev, (int)(A->repoch & 1), (unsigned long long)A->repoch, pp->d_ticket_rev);
+    B200_LAUNCHED(1);
+    *buf_out = pp->rbuf[A->repoch & 1];
+    return 0;
+  }
+  B200_CUDA(cudaEventRecord(c.ev_fork, c.stream));
+  B200_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork, 0));
+  B200_NCCL(g_nccl.GroupStart());
+  for (int k = 0; k < nto; k++)
+    B200_NCCL(g_nccl.Recv(A->d_sendbuf + A->to_starts[k], (size_t)(A->to_starts[k + 1] - A->to_starts[k]), ncclDouble, A->to_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
+  for (int k = 0; k < nfrom; k++)
+    B200_NCCL(g_nccl.Send(ghost_values + A->from_starts[k], (size_t)(A->from_starts[k + 1] - A->from_starts[k]), ncclDouble, A->from_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
+  B200_NCCL(g_nccl.GroupEnd());
+  B200_CUDA(cudaEventRecord(c.ev_join, c.comm_stream));
+  return 0;
+}
+
+/* second half: the compute stream waits until every neighbour's message is in the buffer */
+static int reverse_wait(b200_mat A)
+{
+  B200Ctx &c = g_b200;
+  if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
+  if (A->peerplan) {
+    if (A->nto) {
+      wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->rev, (unsigned long long)A->repoch);
+      B200_LAUNCHED(1);
+    }
+    return 0;
+  }
+  B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
+  return 0;
+}
+
 /* MatMultTranspose_MPIAIJ / MatMultTransposeAdd_MPIAIJ (mpiaij.c:1147-1195): lvec = B^T x ; reverse scatter (ADD) begins ;
  * z = A^T x (+ y) ; scatter ends: every rank adds what its neighbours computed for the rows it owns. */
 int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, double *z)
@@ -600,54 +648,162 @@ int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, do
   if (!A || A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
   B200_CHK(b200_seq_transpose(&A->A));
   B200_CHK(b200_seq_transpose(&A->B));
-  const int nghost = A->nghost, nto = A->nto, nfrom = A->nfrom;
-  const bool exchange = c.size > 1 && (nto || nfrom);
+  const int nghost = A->nghost, nto = A->nto;
   if (!A->d_ghost_t) {
     B200_CUDA(cudaMalloc((void **)&A->d_ghost_t, sizeof(double) * (size_t)(nghost + 2)));
     B200_CUDA(cudaMemset(A->d_ghost_t, 0, sizeof(double) * (size_t)(nghost + 2)));
   }
   if (nghost) { B200_CHK(b200_seq_mult(A->B.T, x, NULL, A->d_ghost_t, false, NULL)); }
-  const double *buf = A->d_sendbuf;
-  A->repoch++;
-  if (exchange) {
-    if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "MPIAIJ MatMultTranspose on %d ranks needs b200_comm_init", c.size);
-    if (A->peerplan) {
-      PeerPlan *pp = (PeerPlan *)A->peerplan;
-      int g = (nghost + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
-      pack_put_kernel<<<g, 256, 0, c.stream>>>(nghost, NULL, A->d_ghost_t, pp->rev, (int)(A->repoch & 1), (unsigned long long)A->repoch, pp->d_ticket_rev);
-      B200_LAUNCHED(1);
-      buf = pp->rbuf[A->repoch & 1];
-    } else {
-      B200_CUDA(cudaEventRecord(c.ev_fork, c.stream));
-      B200_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork, 0));
-      B200_NCCL(g_nccl.GroupStart());
-      for (int k = 0; k < nto; k++)
-        B200_NCCL(g_nccl.Recv(A->d_sendbuf + A->to_starts[k], (size_t)(A->to_starts[k + 1] - A->to_starts[k]), ncclDouble, A->to_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
-      for (int k = 0; k < nfrom; k++)
-        B200_NCCL(g_nccl.Send(A->d_ghost_t + A->from_starts[k], (size_t)(A->from_starts[k + 1] - A->from_starts[k]), ncclDouble, A->from_procs[k], (ncclComm_t)c.nccl, c.comm_stream));
-      B200_NCCL(g_nccl.GroupEnd());
-      B200_CUDA(cudaEventRecord(c.ev_join, c.comm_stream));
-    }
-  }
+  const double *buf = NULL;
+  B200_CHK(reverse_begin(A, A->d_ghost_t, &buf));
   /* local part */
   if (A->A.m == 0) { if (yin && z != yin && A->A.n > 0) B200_CHK(b200_vec_copy(A->A.n, yin, z)); }
   else if (yin) { B200_CHK(b200_seq_mult(A->A.T, x, yin, z, true, NULL)); }
   else { B200_CHK(b200_seq_mult(A->A.T, x, NULL, z, false, NULL)); }
-  if (!exchange) return 0;
-  if (A->peerplan) {
-    if (nto) {
-      wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->rev, (unsigned long long)A->repoch);
-      B200_LAUNCHED(1);
-    }
-  } else {
-    B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));
-  }
+  if (c.size <= 1) return 0;
+  B200_CHK(reverse_wait(A));
   for (int k = 0; k < nto; k++) {
     const int len = A->to_starts[k + 1] - A->to_starts[k];
     if (len <= 0) continue;
     int g = (len + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
     unpack_add_kernel<<<g, 256, 0, c.stream>>>(len, A->d_to_indices + A->to_starts[k], buf + A->to_starts[k], z);
     B200_LAUNCHED(1);
+  }
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------ general VecScatter */
+/* A device-resident VecScatter between a parallel vector (x, this rank's part) and a sequential vector (y): the general
+ * MPI -> Seq case of VecScatterCreate_PtoS (vpscat.c:1730-1924) with VecScatterBegin_1 / End_1 (vpscat.h:14-233) in both
+ * modes (SCATTER_FORWARD x -> y, SCATTER_REVERSE y -> x) and both InsertModes.  The exchange engine is the one the
+ * MPIAIJ operator uses (an operator-shaped object without matrix blocks): forward messages land contiguously in its
+ * ghost vector and are then unpacked to from_indices; reverse messages land in its return buffer and are unpacked to
+ * to_indices.  The self part (entries this rank owns) is a device copy done in Begin like vpscat.h:100-128. */
+struct b200_scatter_s {
+  b200_mat ex;
+  int      nx, ny, nrecv, nsend, nlocal;
+  int     *d_from_indices, *d_to_local, *d_from_local;
+  double  *d_stage;            /* [nrecv] reverse mode: y[from_indices] gathered before it travels                 */
+  bool     dup_from, dup_to, dup_local_from, dup_local_to;   /* repeated targets -> atomic adds               */
+};
+
+template <bool ADD, bool ATOMIC>
+__global__ void __launch_bounds__(256) scatter_store_kernel(int n, const int *__restrict__ dst_idx, const int *__restrict__ src_idx,
+                                                            const double *__restrict__ src, double *dst)
+{
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const double v = src[src_idx ? __ldg(&src_idx[i]) : i];
+    const int r = dst_idx ? __ldg(&dst_idx[i]) : i;
+    if (!ADD) dst[r] = v;
+    else if (ATOMIC) atomicAdd(&dst[r], v);
+    else dst[r] = dst[r] + v;
+  }
+}
+
+static int scatter_store(int n, const int *dst_idx, const int *src_idx, const double *src, double *dst, bool add, bool atomic)
+{
+  if (n <= 0) return 0;
+  int g = (n + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
+  cudaStream_t st = g_b200.stream;
+  if (!add) scatter_store_kernel<false, false><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
+  else if (atomic) scatter_store_kernel<true, true><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
+  else scatter_store_kernel<true, false><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
+  B200_LAUNCHED(1);
+  return 0;
+}
+
+static bool has_dups(const int *v, int n)
+{
+  if (n < 2) return false;
+  std::vector<int> w(v, v + n);
+  std::sort(w.begin(), w.end());
+  for (int i = 1; i < n; i++) if (w[i] == w[i - 1]) return true;
+  return false;
+}
+
+extern "C" int b200_scatter_create(int nx_local, int ny,
+                                   int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                                   int nfrom, const int *from_procs, const int *from_starts, const int *from_indices,
+                                   int nlocal, const int *to_local, const int *from_local, b200_scatter *out)
+{
+  B200_NEED_INIT();
+  if (!out) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
+  *out = NULL;
+  if (nto < 0 || nfrom < 0 || nlocal < 0 || nx_local < 0 || ny < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative size");
+  const int nrecv = nfrom ? from_starts[nfrom] : 0, nsend = nto ? to_starts[nto] : 0;
+  for (int i = 0; i < nsend; i++) if (to_indices[i] < 0 || to_indices[i] >= nx_local) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "send index %d outside the local part [0,%d)", to_indices[i], nx_local);
+  for (int i = 0; i < nrecv; i++) if (from_indices[i] < 0 || from_indices[i] >= ny) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Scattering past end of TO vector");
+  for (int i = 0; i < nlocal; i++)
+    if (to_local[i] < 0 || to_local[i] >= nx_local || from_local[i] < 0 || from_local[i] >= ny) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "local scatter index out of range");
+  b200_scatter S = (b200_scatter)calloc(1, sizeof(*S));
+  if (!S) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  S->nx = nx_local; S->ny = ny; S->nrecv = nrecv; S->nsend = nsend; S->nlocal = nlocal;
+  static const int zero_i[2] = {0, 0};
+  std::vector<int> ghost_ids((size_t)(nrecv > 0 ? nrecv : 1));
+  for (int i = 0; i < nrecv; i++) ghost_ids[i] = i;
+  int rc = b200_mat_create_mpiaij(0, 0, 0, zero_i, NULL, NULL, nrecv, zero_i, NULL, NULL, ghost_ids.data(),
+                                  nto, to_procs, to_starts, to_indices, nfrom, from_procs, from_starts, &S->ex);
+  if (rc) { free(S); return rc; }
+  auto up = [](int **d, const int *h, int n) -> cudaError_t {
+    cudaError_t e = cudaMalloc((void **)d, sizeof(int) * (size_t)(n + 1));
+    if (e == cudaSuccess && n) e = cudaMemcpy(*d, h, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice);
+    return e;
+  };
+  B200_CUDA(up(&S->d_from_indices, from_indices, nrecv));
+  B200_CUDA(up(&S->d_to_local, to_local, nlocal));
+  B200_CUDA(up(&S->d_from_local, from_local, nlocal));
+  B200_CUDA(cudaMalloc((void **)&S->d_stage, sizeof(double) * (size_t)(nrecv + 2)));
+  S->dup_from = has_dups(from_indices, nrecv);
+  S->dup_local_from = has_dups(from_local, nlocal) || S->dup_from;
+  S->dup_local_to = has_dups(to_local, nlocal);
+  S->dup_to = false;
+  for (int k = 0; k < nto && !S->dup_to; k++) S->dup_to = has_dups(to_indices + to_starts[k], to_starts[k + 1] - to_starts[k]);
+  *out = S;
+  return 0;
+}
+
+extern "C" int b200_scatter_destroy(b200_scatter S)
+{
+  if (!S) return 0;
+  b200_mat_destroy(S->ex);
+  cudaFree(S->d_from_indices); cudaFree(S->d_to_local); cudaFree(S->d_from_local); cudaFree(S->d_stage);
+  free(S);
+  return 0;
+}
+
+/* x: this rank's part of the parallel vector (nx_local), y: the sequential vector (ny).  add: 0 INSERT_VALUES, 1 ADD_VALUES;
+ * reverse: 0 SCATTER_FORWARD (x -> y), 1 SCATTER_REVERSE (y -> x). */
+extern "C" int b200_scatter_begin(b200_scatter S, double *x, double *y, int add, int reverse)
+{
+  B200_NEED_INIT();
+  if (!S || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (!reverse) {
+    B200_CHK(b200_mpiaij_exchange_begin(S->ex, x));
+    return scatter_store(S->nlocal, S->d_from_local, S->d_to_local, x, y, add != 0, S->dup_local_from);
+  }
+  B200_CHK(scatter_store(S->nrecv, NULL, S->d_from_indices, y, S->d_stage, false, false));     /* Pack: stage[i] = y[from_indices[i]] */
+  const double *buf = NULL;
+  B200_CHK(reverse_begin(S->ex, S->d_stage, &buf));
+  return scatter_store(S->nlocal, S->d_to_local, S->d_from_local, y, x, add != 0, S->dup_local_to);
+}
+
+extern "C" int b200_scatter_end(b200_scatter S, double *x, double *y, int add, int reverse)
+{
+  B200_NEED_INIT();
+  if (!S || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  b200_mat E = S->ex;
+  if (!reverse) {
+    B200_CHK(b200_mpiaij_exchange_end(E));
+    if (g_b200.size <= 1) return 0;
+    return scatter_store(S->nrecv, S->d_from_indices, NULL, E->d_lvec[E->epoch & 1], y, add != 0, S->dup_from);
+  }
+  if (g_b200.size <= 1) return 0;
+  B200_CHK(reverse_wait(E));
+  const double *buf = E->peerplan ? ((PeerPlan *)E->peerplan)->rbuf[E->repoch & 1] : E->d_sendbuf;
+  for (int k = 0; k < E->nto; k++) {                      /* neighbour by neighbour, ascending rank: fixed summation order */
+    const int len = E->to_starts[k + 1] - E->to_starts[k];
+    B200_CHK(scatter_store(len, E->d_to_indices + E->to_starts[k], NULL, buf + E->to_starts[k], x, add != 0, S->dup_to));
   }
   return 0;
 }

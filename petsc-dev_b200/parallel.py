@@ -179,3 +179,53 @@ def p2p_enabled():
     e = C.c_int()
     _chk(lib.b200_comm_p2p_enabled(C.byref(e)), "b200_comm_p2p_enabled")
     return bool(e.value)
+
+
+class Scatter:
+    """Device-resident VecScatter between this rank's part of a parallel vector and a sequential vector
+    (VecScatterCreate_PtoS + VecScatterBegin/End, both modes and InsertModes)."""
+
+    def __init__(self, handle, nx, ny):
+        self.h, self.nx, self.ny = handle, nx, ny
+
+    def begin(self, x, y, add=False, reverse=False):
+        _chk(lib.b200_scatter_begin(self.h, x.p, y.p, int(bool(add)), int(bool(reverse))), "VecScatterBegin")
+
+    def end(self, x, y, add=False, reverse=False):
+        _chk(lib.b200_scatter_end(self.h, x.p, y.p, int(bool(add)), int(bool(reverse))), "VecScatterEnd")
+
+    def scatter(self, x, y, add=False, reverse=False):
+        self.begin(x, y, add, reverse)
+        self.end(x, y, add, reverse)
+
+    def destroy(self):
+        if self.h:
+            lib.b200_scatter_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.destroy()
+        except Exception:
+            pass
+
+
+def create_scatter(rank, size, ranges, inidx, inidy, ny, bs=1, dist=None, device="cpu"):
+    """VecScatterCreate(x parallel, ix = inidx (global, block ids when bs > 1), y sequential of length ny, iy = inidy)."""
+    rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
+    frm = scatter_plan_from(inidx, inidy, bs, ranges, rank, ny)
+    if size > 1:
+        procs, lengths, req = exchange_requests(frm, rank, size, dist, device)
+    else:
+        procs, lengths, req = np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32)
+    to = scatter_plan_to(procs, lengths, req, rstart, rend)
+    ts, ti = expand_bs(to["to_starts"], to["to_indices"], bs)          # block lists -> scalar entries
+    fs, fi = expand_bs(frm["from_starts"], frm["from_indices"], bs)
+    _, tl = expand_bs(np.zeros(1), frm["to_local"], bs)
+    _, fl = expand_bs(np.zeros(1), frm["from_local"], bs)
+    h = C.c_void_p()
+    tp, fp = _i32(to["to_procs"]), _i32(frm["from_procs"])
+    _chk(lib.b200_scatter_create(rend - rstart, int(ny), int(to["nto"]), _ip(tp), _ip(ts), _ip(ti),
+                                 int(frm["nfrom"]), _ip(fp), _ip(fs), _ip(fi), int(tl.size), _ip(tl), _ip(fl), C.byref(h)),
+         "VecScatterCreate")
+    return Scatter(h, rend - rstart, int(ny))

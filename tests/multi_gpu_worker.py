@@ -134,6 +134,52 @@ def main():
                     res[key] = dict(its=r["its"], ref_its=int(rr["its"]), reason=r["reason"], ref_reason=int(rr["reason"]), hist_dev=dev)
             out["cases"][name] = res
         del A
+    # ---- general device VecScatter (parallel <-> sequential), integer-valued data so every summation order is exact ----
+    sc = {}
+    for bs in (1, 3):
+        N = 999
+        ranges = par.split_ownership(N, world, bs)
+        rs, re_ = int(ranges[rank]), int(ranges[rank + 1])
+        m = re_ - rs
+        rng = np.random.RandomState(100 + rank)
+        nblk = 60
+        inidx = rng.randint(0, N // bs, size=nblk).astype(np.int32)        # block ids, repeats allowed, some owned here
+        inidx[:5] = (rs // bs) + np.arange(5) % max(m // bs, 1)              # force a self part
+        inidy = rng.permutation(nblk).astype(np.int32)                      # distinct positions in the sequential vector
+        ny = nblk * bs
+        S = par.create_scatter(rank, world, ranges, inidx, inidy, ny, bs=bs, dist=dist, device="cuda")
+        xg = np.arange(N, dtype=np.float64) * 3.0 + 1.0
+        y0 = np.arange(ny, dtype=np.float64) * 7.0 + rank
+        gi = (bs * inidx[:, None] + np.arange(bs)[None, :]).reshape(-1)       # scalar global ids
+        yi = (bs * inidy[:, None] + np.arange(bs)[None, :]).reshape(-1)
+        x, y = pb.Vec(m, xg[rs:re_]), pb.Vec(ny, y0)
+        ok = True
+        for _ in range(2):                                                  # both buffer parities
+            S.scatter(x, y)                                                  # forward INSERT
+            want = y0.copy(); want[yi] = xg[gi]
+            ok = ok and np.array_equal(y.get_array(), want)
+        y.set_array(y0)
+        S.scatter(x, y, add=True)                                            # forward ADD
+        want = y0.copy(); np.add.at(want, yi, xg[gi])
+        ok = ok and np.array_equal(y.get_array(), want)
+        # reverse ADD: every rank's y flows back and accumulates on the owners
+        y.set_array(y0)
+        allgi = [torch.zeros(gi.size, dtype=torch.int64, device="cuda") for _ in range(world)]
+        allyv = [torch.zeros(gi.size, dtype=torch.float64, device="cuda") for _ in range(world)]
+        dist.all_gather(allgi, torch.from_numpy(gi.astype(np.int64)).cuda())
+        dist.all_gather(allyv, torch.from_numpy(y0[yi]).cuda())
+        for rep in range(2):
+            x.set_array(xg[rs:re_])
+            S.scatter(x, y, add=True, reverse=True)
+            want = xg.copy()
+            for r in range(world):
+                np.add.at(want, allgi[r].cpu().numpy(), allyv[r].cpu().numpy())
+            ok = ok and np.array_equal(x.get_array(), want[rs:re_])
+        sc["bs%d" % bs] = bool(ok)
+        del S
+    oks = torch.tensor([1.0 if all(sc.values()) else 0.0], device="cuda")
+    dist.all_reduce(oks, op=dist.ReduceOp.MIN)
+    out["scatter"] = dict(sc, all_ranks=bool(oks.item() == 1.0))
     if rank == 0:
         print("MULTI_GPU_RESULT " + json.dumps(out))
     dist.barrier()

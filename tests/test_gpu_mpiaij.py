@@ -52,3 +52,29 @@ def test_virtual_ranks(gpu, R, P, name, size, lanes):
     else:
         assert np.array_equal(got, want)
         assert np.array_equal(got_add, want_add)
+
+
+def test_scatter_single_rank_self_part(gpu, P):
+    """The device VecScatter on one rank is the self part only (vpscat.c:1890-1903): forward/reverse, INSERT/ADD, repeated
+    sources, and the range checks of the constructor."""
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    N, ny = 50, 8
+    ranges = par.split_ownership(N, 1)
+    inidx = np.array([7, 3, 3, 49, 0, 12, 25, 7], np.int32)
+    inidy = np.array([0, 1, 2, 3, 4, 5, 6, 7], np.int32)
+    S = par.create_scatter(0, 1, ranges, inidx, inidy, ny)
+    xh = np.arange(N, dtype=np.float64) + 0.5
+    yh = np.linspace(-1, 1, ny)
+    x, y = gpu.Vec(N, xh), gpu.Vec(ny, yh)
+    S.scatter(x, y)
+    assert np.array_equal(y.get_array(), xh[inidx])
+    y.set_array(yh)
+    S.scatter(x, y, add=True)
+    assert np.array_equal(y.get_array(), yh + xh[inidx])
+    y.set_array(yh)
+    S.scatter(x, y, add=True, reverse=True)                # repeated targets (3 and 7 twice) -> atomic adds
+    want = xh.copy(); np.add.at(want, inidx, yh)
+    assert np.allclose(x.get_array(), want, rtol=0, atol=1e-15)
+    with pytest.raises(gpu.PetscB200Error) as e:
+        par.create_scatter(0, 1, ranges, np.array([1], np.int32), np.array([9], np.int32), ny)
+    assert e.value.code == 63
