@@ -221,10 +221,10 @@ def run_b200(args):
     # ---------------- MatMult (device-resident) ----------------
     for _ in range(max(args.warmup, 3)):
         A.mult(x, y)
-    barrier()
     clocks = ClockSampler(local_rank)
     if rank == 0:
-        clocks.start()
+        clocks.start()               # BEFORE the barrier: spawning the sampler costs rank 0 ~1 ms the other ranks would wait for
+    barrier()
     l0 = pb.launch_count()
     pb.timer_start()
     for _ in range(args.steps):

@@ -539,8 +539,13 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x)
   if (A->peerplan) {
     PeerPlan *pp = (PeerPlan *)A->peerplan;
     int g = (nsend + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
-    pack_put_kernel<<<g, 256, 0, c.stream>>>(nsend, A->d_to_indices, x, pp->dev, (int)(A->epoch & 1), (unsigned long long)A->epoch, pp->d_ticket);
+    /* on the side stream, so that the diagonal-block product (launched next on the compute stream) starts at once and
+     * the two run side by side: the pack kernel is small and short, the persistent product fills the rest of the GPU */
+    B200_CUDA(cudaEventRecord(c.ev_fork, c.stream));
+    B200_CUDA(cudaStreamWaitEvent(c.comm_stream, c.ev_fork, 0));
+    pack_put_kernel<<<g, 256, 0, c.comm_stream>>>(nsend, A->d_to_indices, x, pp->dev, (int)(A->epoch & 1), (unsigned long long)A->epoch, pp->d_ticket);
     B200_LAUNCHED(1);
+    B200_CUDA(cudaEventRecord(c.ev_join, c.comm_stream));
     return 0;
   }
   if (nsend) {
@@ -566,6 +571,7 @@ int b200_mpiaij_exchange_end(b200_mat A)
   B200Ctx &c = g_b200;
   if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
   if (A->peerplan) {
+    B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));        /* x may be overwritten only after the pack kernel read it */
     if (A->nfrom) {
       wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->dev, (unsigned long long)A->epoch);
       B200_LAUNCHED(1);
