@@ -304,3 +304,69 @@ int ref_ksp_solve(void *h, int kind, const char *ksptype, const char *pctype, do
   ierr = VecDestroy(&xv); REFCHK(ierr);
   return 0;
 }
+
+/* ---- PETSc binary files through the reference's own viewer (MatView_SeqAIJ_Binary aij.c:414, MatLoad_SeqAIJ aij.c:4093,
+ * VecView / VecLoad): used to pin petsc-dev_b200/binaryio.py against the real format ---- */
+int ref_mat_write_binary(void *h, const char *path)
+{
+  Mat            A = (Mat)h;
+  PetscViewer    v;
+  PetscErrorCode ierr;
+  ierr = PetscViewerBinaryOpen(PETSC_COMM_SELF, path, FILE_MODE_WRITE, &v); REFCHK(ierr);
+  ierr = MatView(A, v); REFCHK(ierr);
+  ierr = PetscViewerDestroy(&v); REFCHK(ierr);
+  return 0;
+}
+
+int ref_mat_load_binary(const char *path, void **out)
+{
+  Mat            A;
+  PetscViewer    v;
+  PetscErrorCode ierr;
+  ierr = ref_initialize(); REFCHK(ierr);
+  ierr = PetscViewerBinaryOpen(PETSC_COMM_SELF, path, FILE_MODE_READ, &v); REFCHK(ierr);
+  ierr = MatCreate(PETSC_COMM_SELF, &A); REFCHK(ierr);
+  ierr = MatSetType(A, MATSEQAIJ); REFCHK(ierr);
+  ierr = MatLoad(A, v); REFCHK(ierr);
+  ierr = PetscViewerDestroy(&v); REFCHK(ierr);
+  *out = (void *)A;
+  return 0;
+}
+
+int ref_vec_write_binary(int n, const double *x, const char *path)
+{
+  Vec            xv;
+  PetscViewer    v;
+  PetscErrorCode ierr;
+  ierr = ref_initialize(); REFCHK(ierr);
+  ierr = VecCreateSeqWithArray(PETSC_COMM_SELF, 1, n, x, &xv); REFCHK(ierr);
+  ierr = PetscViewerBinaryOpen(PETSC_COMM_SELF, path, FILE_MODE_WRITE, &v); REFCHK(ierr);
+  ierr = VecView(xv, v); REFCHK(ierr);
+  ierr = PetscViewerDestroy(&v); REFCHK(ierr);
+  ierr = VecDestroy(&xv); REFCHK(ierr);
+  return 0;
+}
+
+/* n_inout: capacity on entry, the vector's length on return */
+int ref_vec_load_binary(const char *path, int *n_inout, double *x)
+{
+  Vec            xv;
+  PetscViewer    v;
+  PetscScalar    *arr;
+  PetscInt       n;
+  PetscErrorCode ierr;
+  ierr = ref_initialize(); REFCHK(ierr);
+  ierr = PetscViewerBinaryOpen(PETSC_COMM_SELF, path, FILE_MODE_READ, &v); REFCHK(ierr);
+  ierr = VecCreate(PETSC_COMM_SELF, &xv); REFCHK(ierr);
+  ierr = VecSetType(xv, VECSEQ); REFCHK(ierr);
+  ierr = VecLoad(xv, v); REFCHK(ierr);
+  ierr = PetscViewerDestroy(&v); REFCHK(ierr);
+  ierr = VecGetLocalSize(xv, &n); REFCHK(ierr);
+  if (n > *n_inout) { VecDestroy(&xv); *n_inout = (int)n; return 60; }
+  ierr = VecGetArray(xv, &arr); REFCHK(ierr);
+  memcpy(x, arr, sizeof(double) * (size_t)n);
+  ierr = VecRestoreArray(xv, &arr); REFCHK(ierr);
+  *n_inout = (int)n;
+  ierr = VecDestroy(&xv); REFCHK(ierr);
+  return 0;
+}

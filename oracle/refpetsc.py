@@ -197,3 +197,32 @@ def vec_elementwise(op, n, a=0.0, b=0.0, c=0.0, x=None, y=None, w=None):
     """In-place on the given float64 arrays (caller passes copies); see ref_driver.c for operand roles."""
     _chk(lib().ref_vec_elementwise(int(op), int(n), C.c_double(a), C.c_double(b), C.c_double(c), _dp(x), _dp(y),
                                    _dp(w)), "Vec elementwise op %d" % op)
+
+
+def mat_write_binary(mat, path):
+    _chk(lib().ref_mat_write_binary(mat.h, str(path).encode()), "MatView (binary)")
+
+
+def mat_load_binary(path):
+    """MatLoad through the reference -> RefMat (sequential)."""
+    h = C.c_void_p()
+    _chk(lib().ref_mat_load_binary(str(path).encode(), C.byref(h)), "MatLoad")
+    r = RefMat.__new__(RefMat)
+    r.kind, r.h = 0, h
+    m, nz = C.c_int(), C.c_int()
+    lib().ref_mat_get_csr(h, C.byref(m), C.byref(nz), None, None, None)
+    r.m = m.value
+    r.n = None
+    return r
+
+
+def vec_write_binary(x, path):
+    x = _f64(x)
+    _chk(lib().ref_vec_write_binary(int(x.size), _dp(x), str(path).encode()), "VecView (binary)")
+
+
+def vec_load_binary(path, capacity):
+    x = np.empty(int(capacity), np.float64)
+    n = C.c_int(int(capacity))
+    _chk(lib().ref_vec_load_binary(str(path).encode(), C.byref(n), _dp(x)), "VecLoad")
+    return x[:n.value].copy()
