@@ -178,3 +178,24 @@ def test_c2_cg_256_cubed_properties(gpu, P):
     res0 = gpu.ksp_solve(A, b, x, ksp_type="cg", pc_type="jacobi", rtol=1e-8, max_it=3000, fused=0)
     assert res0["its"] == res["its"]
     assert _hist_dev(res["history"], res0["history"]) <= 1e-9
+
+
+def test_ex10_style_binary_file_solve(gpu, R, P, tmp_path):
+    """A matrix file written by the REFERENCE's binary viewer, loaded with petsc-dev_b200/binaryio.py, solved on the B200
+    by tools/ex10_b200.py: iteration count and residual history follow the reference's KSPSolve on the same matrix."""
+    import subprocess, sys, os, re
+    n = 10 ** 3
+    ip, j, a = P.laplace3d_7pt(10)
+    ref = R.RefMat(n, n, ip, j, a, no_inode=True)
+    f = str(tmp_path / "lap7.bin")
+    R.mat_write_binary(ref, f)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, os.path.join(root, "tools", "ex10_b200.py"), "-f0", f, "-ksp_type", "cg", "-pc_type", "jacobi",
+                          "-ksp_rtol", "1e-8", "-ksp_monitor"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    hist = np.array([float(m.group(1)) for m in re.finditer(r"KSP Residual norm (\S+)", out.stdout)])
+    its = int(re.search(r"Number of iterations = +(\d+)", out.stdout).group(1))
+    rr = ref.ksp_solve(ref.mult(np.ones(n)), "cg", "jacobi", rtol=1e-8)
+    assert abs(its - rr["its"]) <= 1
+    k = min(len(hist), len(rr["history"]))
+    assert np.max(np.abs(hist[:k] - rr["history"][:k]) / rr["history"][:k]) < 1e-10

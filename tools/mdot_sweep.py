@@ -1,0 +1,20 @@
+#!/usr/bin/env python3
+"""Development tool: VecMDot / VecMAXPY achieved GB/s for every vector count 1..32 (n = 256^3)."""
+import importlib, os, sys
+import numpy as np
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+pb = importlib.import_module("petsc-dev_b200"); P = importlib.import_module("petsc-dev_b200.problems")
+pb.init(0)
+n = 256 ** 3
+x, y = pb.Vec(n, P.random_vector(n, 1)), pb.Vec(n, P.random_vector(n, 2))
+vs = [pb.Vec(n, P.random_vector(n, 10 + k)) for k in range(32)]
+al = np.linspace(1e-4, 1e-3, 32)
+for nv in range(1, 33):
+    res = []
+    for f, bpe in ((lambda: x.mdot(vs[:nv]), 8 * (nv + 1)), (lambda: y.maxpy(al[:nv], vs[:nv]), 8 * (nv + 2))):
+        for _ in range(2): f()
+        pb.synchronize(); pb.timer_start()
+        for _ in range(10): f()
+        ms = pb.timer_stop() / 10
+        res.append((ms, bpe * n / ms / 1e6))
+    print("nv %2d  mdot %.4f ms %6.0f GB/s   maxpy %.4f ms %6.0f GB/s" % (nv, res[0][0], res[0][1], res[1][0], res[1][1]), flush=True)
