@@ -191,8 +191,8 @@ def run_b200(args):
     else:
         import torch
         par.comm_init(rank, world, dist, device="cuda")
-        if args.transport == "p2p":
-            par.enable_p2p()
+        if args.transport == "p2p" and not par.enable_p2p(strict=False):
+            args.transport = "nccl"          # agreed on by all ranks inside the library; reported in config.transport
         ranges = par.split_ownership(Nglob, world)
         ai, aj, aa = P.laplace3d_7pt(nx, nx, nx * world, r0=int(ranges[rank]), r1=int(ranges[rank + 1]))
         host = par.setup_mpiaij_host(rank, world, ranges, ai - ai[0], aj, aa, Nglob, dist=dist, device="cuda")

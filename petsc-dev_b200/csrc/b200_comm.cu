@@ -232,18 +232,37 @@ extern "C" int b200_comm_enable_p2p(int enable)
           return b200_seterr(B200_ERR_SUP, "ranks %d and %d share GPU %s: the peer-memory transport needs one GPU per rank (use the NCCL transport)", a, b, busid[1 + a]);
         }
   }
+  /* map every peer's arena; the outcome is agreed on collectively (a rank that cannot map a peer must not leave the
+   * others waiting in a barrier it never reaches): all ranks succeed, or all ranks undo and report the same error */
+  int okflag = 1, badrank = -1;
+  cudaError_t bad = cudaSuccess;
   for (int r = 0; r < c.size; r++) {
     if (r == c.rank) { P->peer[r] = P->arena; continue; }
     cudaError_t ce = cudaIpcOpenMemHandle((void **)&P->peer[r], all[r], cudaIpcMemLazyEnablePeerAccess);
-    if (ce != cudaSuccess) return b200_seterr(B200_ERR_LIB, "cudaIpcOpenMemHandle for rank %d: %s (no NVLink peer access?)", r, cudaGetErrorString(ce));
+    if (ce != cudaSuccess) { okflag = 0; bad = ce; badrank = r; P->peer[r] = NULL; cudaGetLastError(); break; }
   }
-  unsigned long long *tab[B200_MAX_RANKS];
-  for (int r = 0; r < c.size; r++) tab[r] = reinterpret_cast<unsigned long long *>(P->peer[r]);
-  B200_CUDA(cudaMalloc((void **)&P->d_inbox, sizeof(tab)));
-  B200_CUDA(cudaMemcpy(P->d_inbox, tab, sizeof(void *) * (size_t)c.size, cudaMemcpyHostToDevice));
+  if (okflag) {
+    unsigned long long *tab[B200_MAX_RANKS];
+    for (int r = 0; r < c.size; r++) tab[r] = reinterpret_cast<unsigned long long *>(P->peer[r]);
+    if (cudaMalloc((void **)&P->d_inbox, sizeof(tab)) != cudaSuccess ||
+        cudaMemcpy(P->d_inbox, tab, sizeof(void *) * (size_t)c.size, cudaMemcpyHostToDevice) != cudaSuccess) { okflag = 0; cudaGetLastError(); }
+  }
+  {
+    int *dflag = NULL, agreed = 0;
+    B200_CUDA(cudaMalloc((void **)&dflag, sizeof(int)));
+    B200_CUDA(cudaMemcpy(dflag, &okflag, sizeof(int), cudaMemcpyHostToDevice));
+    B200_NCCL(g_nccl.AllReduce(dflag, dflag, 1, ncclInt, ncclMin, (ncclComm_t)c.nccl, c.stream));
+    B200_CUDA(cudaStreamSynchronize(c.stream));                   /* doubles as the barrier: every arena is zeroed and mapped */
+    B200_CUDA(cudaMemcpy(&agreed, dflag, sizeof(int), cudaMemcpyDeviceToHost));
+    cudaFree(dflag);
+    if (!agreed) {
+      for (int r = 0; r < c.size; r++) if (r != c.rank && P->peer[r]) cudaIpcCloseMemHandle(P->peer[r]);
+      cudaFree(P->d_inbox); cudaFree(P->arena); free(P);
+      if (!okflag && badrank >= 0) return b200_seterr(B200_ERR_LIB, "cudaIpcOpenMemHandle for rank %d: %s (no NVLink peer access?); the NCCL transport stays in use", badrank, cudaGetErrorString(bad));
+      return b200_seterr(B200_ERR_LIB, "another rank could not map the peer arenas; the NCCL transport stays in use");
+    }
+  }
   c.peer = P;
-  /* everyone's arena must be zeroed and mapped before the first store lands */
-  B200_CHK(b200_comm_barrier());
   c.p2p = true;
   return 0;
 }

@@ -169,10 +169,16 @@ def comm_init(rank, size, dist=None, device=None):
     _chk(lib.b200_comm_init(int(rank), int(size), buf), "b200_comm_init")
 
 
-def enable_p2p(rank=None, size=None, dist=None):
+def enable_p2p(rank=None, size=None, dist=None, strict=True):
     """Switch the ghost exchange and the scalar allreduces to NVLink peer memory (collective; after comm_init).  The
-    CUDA IPC handles travel over the library's own NCCL communicator, so nothing is needed from the host program."""
-    _chk(lib.b200_comm_enable_p2p(1), "b200_comm_enable_p2p")
+    CUDA IPC handles travel over the library's own NCCL communicator, so nothing is needed from the host program.  The
+    library agrees on the outcome across ranks: either every rank is switched, or none is and every rank gets the same
+    error (strict=False: return False instead of raising, the NCCL transport stays in use everywhere)."""
+    rc = lib.b200_comm_enable_p2p(1)
+    if rc and not strict:
+        return False
+    _chk(rc, "b200_comm_enable_p2p")
+    return True
 
 
 def p2p_enabled():

@@ -51,7 +51,9 @@ PetscErrorCode PetscB200Register(void)
       ierr = MPI_Bcast(id,B200_COMM_ID_BYTES,MPI_CHAR,0,PETSC_COMM_WORLD);CHKERRQ(ierr);
       if (b200_comm_init((int)rank,(int)size,id)) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_comm_init: %s",b200_last_error());
       ierr = PetscOptionsGetBool(PETSC_NULL,"-b200_p2p",&p2p,PETSC_NULL);CHKERRQ(ierr);
-      if (p2p && b200_comm_enable_p2p(1)) SETERRQ1(PETSC_COMM_SELF,PETSC_ERR_LIB,"b200_comm_enable_p2p: %s",b200_last_error());
+      if (p2p && b200_comm_enable_p2p(1)) {     /* the library agrees on the outcome across ranks: all switched, or none */
+        ierr = PetscInfo1(0,"B200 peer-memory transport unavailable (%s); using NCCL send/recv\n",b200_last_error());CHKERRQ(ierr);
+      }
     }
   }
   ierr = VecRegister(VECSEQB200,0,"VecCreate_SeqB200",VecCreate_SeqB200);CHKERRQ(ierr);
