@@ -149,3 +149,56 @@ def test_gloo_world_size_2(P):
             assert np.array_equal(to[k], S[r][k]), k
         for k in ("from_procs", "from_starts"):
             assert np.array_equal(frm[k], S[r][k]), k
+
+
+def _gloo_scatter_worker(rank, size, port, q):
+    sys.path.insert(0, ROOT)
+    import torch.distributed as td
+    td.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=size)
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    N, bs = 120, 3
+    ranges = par.split_ownership(N, size, bs)
+    rng = np.random.RandomState(7 + rank)
+    inidx = rng.randint(0, N // bs, size=25).astype(np.int32)          # block ids, repeats allowed
+    inidy = rng.permutation(25).astype(np.int32)
+    frm = par.scatter_plan_from(inidx, inidy, bs, ranges, rank, 25 * bs)
+    procs, lengths, req = par.exchange_requests(frm, rank, size)
+    to = par.scatter_plan_to(procs, lengths, req, int(ranges[rank]), int(ranges[rank + 1]))
+    q.put((rank, inidx, inidy, {k: np.asarray(v) for k, v in frm.items()}, {k: np.asarray(v) for k, v in to.items()}))
+    td.barrier()
+    td.destroy_process_group()
+
+
+def test_gloo_general_scatter_plan(pb):
+    """VecScatterCreate_PtoS for arbitrary (repeated, unsorted, partly local) block indices over 2 gloo ranks: what every
+    owner is asked to send equals, requester by requester in ascending rank, what the requesters' receive lists expect."""
+    import torch.multiprocessing as mp
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_scatter_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    got = {}
+    for _ in range(2):
+        r, inidx, inidy, frm, to = q.get(timeout=120)
+        got[r] = (inidx, inidy, frm, to)
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    N, bs = 120, 3
+    ranges = par.split_ownership(N, 2, bs)
+    for r in range(2):
+        inidx, inidy, frm, to = got[r]
+        o = 1 - r
+        owned = (bs * inidx >= ranges[r]) & (bs * inidx < ranges[r + 1])
+        # self part, in list order (vpscat.c:1890-1903)
+        assert np.array_equal(frm["to_local"], bs * inidx[owned] - ranges[r]) and np.array_equal(frm["from_local"], bs * inidy[owned])
+        # remote part: requests in list order, receive positions alongside
+        assert int(frm["nfrom"]) == (1 if (~owned).any() else 0)
+        assert np.array_equal(frm["req_values"], bs * inidx[~owned]) and np.array_equal(frm["from_indices"], bs * inidy[~owned])
+        # the owner's send list is exactly that request, rebased to its range
+        oto = got[o][3]
+        if (~owned).any():
+            assert list(oto["to_procs"]) == [r]
+            assert np.array_equal(oto["to_indices"], bs * inidx[~owned] - ranges[o])
+            assert list(oto["to_starts"]) == [0, int((~owned).sum())]
