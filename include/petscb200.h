@@ -71,6 +71,9 @@ int         b200_version(void);
 int         b200_device_count(int *n);
 int         b200_set_stream(void *cuda_stream);    /* run on the caller's stream (NULL = the library's own)         */
 int         b200_get_stream(void **cuda_stream);
+int         b200_stream_create(void **cuda_stream);   /* caller-owned non-blocking stream for b200_set_stream (double buffering) */
+int         b200_stream_destroy(void *cuda_stream);
+int         b200_stream_synchronize(void *cuda_stream);
 int         b200_synchronize(void);                /* WaitForGPU, src/vec/vec/impls/seq/seqcusp/cuspvecimpl.h:88    */
 int         b200_launch_count(long long *n);       /* number of kernels this library has launched so far           */
 int         b200_timer_start(void);                /* cudaEventRecord on the compute stream                         */

@@ -70,6 +70,30 @@ def synchronize():
     _chk(lib.b200_synchronize(), "b200_synchronize")
 
 
+class Stream:
+    """A caller-owned CUDA stream; `with stream:` makes the library run on it (b200_set_stream)."""
+
+    def __init__(self):
+        p = C.c_void_p()
+        _chk(lib.b200_stream_create(C.byref(p)), "cudaStreamCreate")
+        self.p = p
+
+    def use(self):
+        _chk(lib.b200_set_stream(self.p), "b200_set_stream")
+
+    def synchronize(self):
+        _chk(lib.b200_stream_synchronize(self.p), "cudaStreamSynchronize")
+
+    def destroy(self):
+        if self.p:
+            lib.b200_stream_destroy(self.p)
+            self.p = None
+
+
+def use_default_stream():
+    _chk(lib.b200_set_stream(None), "b200_set_stream")
+
+
 def launch_count():
     n = C.c_longlong()
     lib.b200_launch_count(C.byref(n))
@@ -114,6 +138,13 @@ class Vec:
             raise PetscB200Error(60, "VecSetValues size")
         _chk(lib.b200_memcpy_h2d(C.c_void_p(self.ptr), h.ctypes.data_as(C.c_void_p), C.c_size_t(8 * self.n)), "H2D")
         return self
+
+    def set_array_async(self, pinned):
+        """Stream-ordered H2D from a pinned numpy array (pinned_array); returns at once."""
+        _chk(lib.b200_memcpy_h2d_async(C.c_void_p(self.ptr), pinned.ctypes.data_as(C.c_void_p), C.c_size_t(8 * self.n)), "H2D async")
+
+    def get_array_async(self, pinned):
+        _chk(lib.b200_memcpy_d2h_async(pinned.ctypes.data_as(C.c_void_p), C.c_void_p(self.ptr), C.c_size_t(8 * self.n)), "D2H async")
 
     def get_array(self, out=None):
         out = np.empty(self.n, np.float64) if out is None else out

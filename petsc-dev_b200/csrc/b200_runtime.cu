@@ -104,6 +104,33 @@ extern "C" int b200_get_stream(void **s)
   return 0;
 }
 
+/* caller-owned streams (for b200_set_stream): lets a host program double-buffer, e.g. upload the next vector while the
+ * previous result is still on its way back */
+extern "C" int b200_stream_create(void **s)
+{
+  B200_NEED_INIT();
+  if (!s) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  cudaStream_t st;
+  B200_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  *s = (void *)st;
+  return 0;
+}
+
+extern "C" int b200_stream_destroy(void *s)
+{
+  if (!s) return 0;
+  if (g_b200.inited && g_b200.stream == (cudaStream_t)s) g_b200.stream = g_b200.own_stream;
+  B200_CUDA(cudaStreamDestroy((cudaStream_t)s));
+  return 0;
+}
+
+extern "C" int b200_stream_synchronize(void *s)
+{
+  B200_NEED_INIT();
+  B200_CUDA(cudaStreamSynchronize(s ? (cudaStream_t)s : g_b200.own_stream));
+  return 0;
+}
+
 extern "C" int b200_synchronize(void)
 {
   B200_NEED_INIT();
