@@ -318,7 +318,7 @@ __global__ void __launch_bounds__(256) pack_put_kernel(int nsend, const int *__r
   if (tid <= plan.nto) s_starts[tid] = plan.to_starts[tid];
   if (tid < plan.nto) {
     s_dst[tid] = plan.dst[parity * plan.nto + tid];
-    while (ld_acquire_sys(plan.lcredit[tid]) + 2 < epoch) { }
+    { const long long t0 = clock64(); while (ld_acquire_sys(plan.lcredit[tid]) + 2 < epoch) b200_spin_guard(t0); }
   }
   __syncthreads();
   const int stride = gridDim.x * blockDim.x;
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(256) pack_put_kernel(int nsend, const int *__r
 /* VecScatterEnd: one warp waits until every sender's flag shows this exchange */
 __global__ void __launch_bounds__(32) wait_arrivals_kernel(const PeerPlanDev plan, unsigned long long epoch)
 {
-  if ((int)threadIdx.x < plan.nfrom) while (ld_acquire_sys(plan.lflag[threadIdx.x]) < epoch) { }
+  if ((int)threadIdx.x < plan.nfrom) { const long long t0 = clock64(); while (ld_acquire_sys(plan.lflag[threadIdx.x]) < epoch) b200_spin_guard(t0); }
 }
 
 static void peerplan_free(b200_mat M)

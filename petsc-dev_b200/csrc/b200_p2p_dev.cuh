@@ -25,6 +25,14 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double *p)
   return v;
 }
 
+/* Every wait on a peer is bounded: a rank that died (or a collective called out of order) must end in a loud failure
+ * (the kernel traps, the next CUDA call reports it), never in a GPU that spins for ever.  ~60 s of SM cycles. */
+#define B200_SPIN_LIMIT_CYCLES (120ll * 1000ll * 1000ll * 1000ll)
+__device__ __forceinline__ void b200_spin_guard(long long t0)
+{
+  if (clock64() - t0 > B200_SPIN_LIMIT_CYCLES) __trap();
+}
+
 /* Called by ALL threads of one CTA (>= 64 threads).  Thread t < size stores this rank's n values into rank t's inbox
  * slot [seq parity][rank], fences, stores the sequence number, then waits for rank t's slot here; the values are then
  * summed (or maxed) in rank order — bitwise the same on every rank — back into vals[0..n).  n <= P2P_AR_MAXV.
@@ -42,7 +50,7 @@ __device__ __forceinline__ void b200_p2p_allreduce_cta(double *vals, int n, int 
     __threadfence_system();
     st_release_sys(slot, seq);
     const unsigned long long *mine = inbox[rank] + par + (size_t)t * P2P_AR_SLOT;
-    while (ld_acquire_sys(mine) != seq) { }
+    { const long long t0 = clock64(); while (ld_acquire_sys(mine) != seq) b200_spin_guard(t0); }
   }
   __syncthreads();
   if (t < n) {
