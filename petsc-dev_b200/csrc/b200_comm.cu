@@ -17,6 +17,11 @@
  *     exchange it has consumed), so non-symmetric neighbour graphs cannot overrun a buffer.
  *   - allreduce of the Krylov scalars = one tiny kernel: every rank stores its values into every peer's inbox slot,
  *     fences, stores the sequence number; each rank then sums the slots in rank order (bitwise identical everywhere).
+ *   - the same engine runs backwards (reverse_begin / reverse_wait): ghost-side contributions travel to their owners'
+ *     return buffers and are added neighbour by neighbour in ascending rank order — MatMultTranspose_MPIAIJ
+ *     (mpiaij.c:1147) and SCATTER_REVERSE/ADD_VALUES of the general b200_scatter (end of this file), which is an
+ *     operator-shaped exchange object without matrix blocks plus unpack kernels for arbitrary index lists.
+ *   - every wait on a peer is bounded (b200_spin_guard): a dead rank ends in a trap, not in a GPU that spins for ever.
  */
 #include "b200_internal.h"
 #include <dlfcn.h>
