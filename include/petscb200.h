@@ -140,6 +140,24 @@ int b200_vec_dotnorm2(int n, const double *s, const double *t, double *dp_host, 
  * (src/mat/impls/aij/seq/seqcusp/aijcusp.cu:126,458).  The host arrays are not retained. */
 int b200_mat_create_seqaij(int m, int n, const int *i_host, const int *j_host, const double *a_host, b200_mat *A);
 int b200_mat_update_values(b200_mat A, const double *a_host);    /* same pattern, new values (value-only re-upload) */
+/* Device assembly: MatSetValuesBatch (src/mat/interface/matrix.c:1698; the reference's device version is
+ * MatSetValuesBatch_SeqAIJCUSP, src/mat/impls/aij/seq/seqcusp/aijAssemble.cu:157-290).  ne element matrices of nl x nl
+ * values (row-major, concatenated in elem_mats) are added into the rows/columns elem_rows[e*nl .. e*nl+nl) of a new
+ * m x n SeqAIJ matrix.  The result is what the reference's host path builds with one MatSetValues(..., ADD_VALUES)
+ * per element on an empty matrix (matrix.c:1712-1716): same i/j (explicit zeros kept, aij.c:293-368), and every value
+ * is the sum of its contributions in element order, left to right — bit-identical.  Negative row / column ids are
+ * skipped (aij.c:311,325); ids beyond the matrix are an error (B200_ERR_ARG_OUTOFRANGE).
+ * on_device != 0: elem_rows / elem_mats are device pointers (no host<->device traffic except the m+1 row offsets).
+ * keep_plan != 0: the element -> nonzero plan stays with the matrix and b200_mat_setvaluesbatch_values refills the
+ * values from a new elem_mats (same elem_rows) without sorting again — the "same pattern, new values" fast path of a
+ * time-dependent or nonlinear loop (replaces the full re-upload of aijcusp.cu:138-152).
+ * Limit: ne*nl*nl < 2^31 - 1 per matrix (per GPU). */
+int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                            int on_device, int keep_plan, b200_mat *A);
+int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mats, int on_device);
+/* Copy the device CSR of a sequential matrix back to host arrays (i: m+1, j/a: nz; any may be NULL) —
+ * MatCUSPCopyFromGPU, aijcusp.cu:187. */
+int b200_mat_get_csr(b200_mat A, int *i_host, int *j_host, double *a_host);
 int b200_mat_destroy(b200_mat A);
 int b200_mat_get_size(b200_mat A, int *m, int *n, long long *nz);
 int b200_mat_mult(b200_mat A, const double *x, double *y);                    /* MatMult_SeqAIJ aij.c:1225 / MatMult_MPIAIJ mpiaij.c:1102       */

@@ -370,3 +370,24 @@ int ref_vec_load_binary(const char *path, int *n_inout, double *x)
   ierr = VecDestroy(&xv); REFCHK(ierr);
   return 0;
 }
+
+/* MatSetValuesBatch (src/mat/interface/matrix.c:1698) on a fresh SeqAIJ matrix through the reference's host path: the
+ * type has no setvaluesbatch op, so matrix.c:1712-1716 issues one MatSetValues(..., ADD_VALUES) per element.
+ * nnz_hint[m] preallocates the rows (an upper bound keeps the run free of reallocations; the assembled result does not
+ * depend on it).  The assembled matrix is returned as a handle for ref_mat_get_csr / ref_mat_mult. */
+int ref_mat_setvaluesbatch(int m, int n, int ne, int nl, int *rows, const double *vals, const int *nnz_hint, void **out)
+{
+  Mat            A;
+  PetscErrorCode ierr;
+  ierr = ref_initialize(); REFCHK(ierr);
+  ierr = MatCreate(PETSC_COMM_SELF, &A); REFCHK(ierr);
+  ierr = MatSetSizes(A, m, n, m, n); REFCHK(ierr);
+  ierr = MatSetType(A, MATSEQAIJ); REFCHK(ierr);
+  ierr = MatSeqAIJSetPreallocation(A, 0, nnz_hint); REFCHK(ierr);
+  ierr = MatSetOption(A, MAT_NEW_NONZERO_ALLOCATION_ERR, PETSC_FALSE); REFCHK(ierr);
+  ierr = MatSetValuesBatch(A, ne, nl, rows, vals); REFCHK(ierr);
+  ierr = MatAssemblyBegin(A, MAT_FINAL_ASSEMBLY); REFCHK(ierr);
+  ierr = MatAssemblyEnd(A, MAT_FINAL_ASSEMBLY); REFCHK(ierr);
+  *out = (void *)A;
+  return 0;
+}

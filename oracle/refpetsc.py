@@ -226,3 +226,19 @@ def vec_load_binary(path, capacity):
     n = C.c_int(int(capacity))
     _chk(lib().ref_vec_load_binary(str(path).encode(), C.byref(n), _dp(x)), "VecLoad")
     return x[:n.value].copy()
+
+
+def mat_setvaluesbatch(m, n, elem_rows, elem_mats, nl):
+    """MatSetValuesBatch (matrix.c:1698) on an empty SeqAIJ through the reference's host path (one MatSetValues with
+    ADD_VALUES per element) -> RefMat.  elem_rows: ne*nl ids, elem_mats: ne*nl*nl values."""
+    rows = _i32(elem_rows).copy()
+    vals = _f64(elem_mats)
+    ne = rows.size // nl
+    assert rows.size == ne * nl and vals.size == ne * nl * nl
+    ok = (rows >= 0) & (rows < m)
+    hint = np.minimum(np.bincount(rows[ok], minlength=m).astype(np.int64) * nl, n).astype(np.int32)
+    h = C.c_void_p()
+    _chk(lib().ref_mat_setvaluesbatch(int(m), int(n), int(ne), int(nl), _ip(rows), _dp(vals), _ip(hint), C.byref(h)), "MatSetValuesBatch")
+    r = RefMat.__new__(RefMat)
+    r.kind, r.h, r.m, r.n = 0, h, int(m), int(n)
+    return r

@@ -275,6 +275,42 @@ class Mat:
         aa = _f64(aa)
         _chk(lib.b200_mat_update_values(self.h, _dp(aa)), "MatAssemblyEnd (values)")
 
+    @classmethod
+    def set_values_batch(cls, m, n, nl, elem_rows, elem_mats, keep_plan=False):
+        """MatSetValuesBatch (matrix.c:1698) on the device: ne element matrices of nl x nl values added into the rows and
+        columns elem_rows[e*nl:(e+1)*nl] of a new m x n matrix.  Host arrays in, device matrix out."""
+        rows, vals = _i32(elem_rows), _f64(elem_mats)
+        ne = rows.size // int(nl)
+        if rows.size != ne * nl or vals.size != ne * nl * nl:
+            raise ValueError("elem_rows must hold ne*nl ids and elem_mats ne*nl*nl values")
+        h = C.c_void_p()
+        _chk(lib.b200_mat_setvaluesbatch(int(m), int(n), C.c_longlong(ne), int(nl), _ip(rows), _dp(vals), 0, int(bool(keep_plan)),
+                                         C.byref(h)), "MatSetValuesBatch")
+        return cls(h, m, n)
+
+    @classmethod
+    def set_values_batch_device(cls, m, n, ne, nl, elem_rows_dev, elem_mats_dev, keep_plan=False):
+        """Same with the element arrays already on the device (raw device pointers: int32 ids, float64 values)."""
+        h = C.c_void_p()
+        _chk(lib.b200_mat_setvaluesbatch(int(m), int(n), C.c_longlong(int(ne)), int(nl), C.c_void_p(int(elem_rows_dev)),
+                                         C.c_void_p(int(elem_mats_dev)), 1, int(bool(keep_plan)), C.byref(h)), "MatSetValuesBatch")
+        return cls(h, m, n)
+
+    def batch_values(self, elem_mats):
+        """Same elem_rows, new element matrices: refill the values through the kept plan (host array)."""
+        vals = _f64(elem_mats)
+        _chk(lib.b200_mat_setvaluesbatch_values(self.h, _dp(vals), 0), "MatSetValuesBatch (values)")
+
+    def batch_values_device(self, elem_mats_dev):
+        _chk(lib.b200_mat_setvaluesbatch_values(self.h, C.c_void_p(int(elem_mats_dev)), 1), "MatSetValuesBatch (values)")
+
+    def csr(self):
+        """Device CSR copied back to the host: (i, j, a)."""
+        nz = self.nnz()
+        i, j, a = np.empty(self.m + 1, np.int32), np.empty(nz, np.int32), np.empty(nz, np.float64)
+        _chk(lib.b200_mat_get_csr(self.h, _ip(i), _ip(j), _dp(a)), "MatCUSPCopyFromGPU")
+        return i, j, a
+
     def destroy(self):
         if self.h:
             lib.b200_mat_destroy(self.h)

@@ -1,0 +1,464 @@
+/* Device assembly of a SeqAIJ matrix from element matrices: MatSetValuesBatch (src/mat/interface/matrix.c:1698).
+ *
+ * What the reference does.  Host path (matrix.c:1712-1716): one MatSetValues(A, nl, rows_e, nl, rows_e, v_e, ADD_VALUES)
+ * per element; MatSetValues_SeqAIJ (aij.c:293-368) walks the nl rows of the block in order, and within a row the nl
+ * columns in order, inserting a new nonzero (sorted position, value = v) or adding to the existing one.  So a nonzero
+ * (r, c) ends up holding  ((v_0 + v_1) + v_2) + ...  with its contributions ordered by (element, row-in-element,
+ * column-in-element), explicit zeros stay in the pattern, negative ids are skipped.  Device path of the reference
+ * (MatSetValuesBatch_SeqAIJCUSP, aijAssemble.cu:157-290): expand to a fat COO, global sort by (i, j), reduce by key,
+ * COO -> CSR, copy back.
+ *
+ * What this file does instead (no global sort, no fat COO in memory).  Every use of a row id in elem_rows is an
+ * "occurrence" o = e*nl + a; it contributes the nl fat entries (elem_rows[e*nl + b], elem_mats[o*nl + b]), b = 0..nl-1.
+ *   1. count the occurrences of every row (atomics), exclusive scan -> occurrence offsets            [4 B / occurrence]
+ *   2. fill the per-row occurrence lists (atomic cursors: arbitrary order inside a row)              [8 B / occurrence]
+ *   3. one warp per row (one CTA for rows with more than 512 fat entries): sort the row's occurrences ascending
+ *      (this restores the element order, so the result does not depend on the atomics), expand them to fat keys
+ *      (column << 32 | position) in shared memory, bitonic sort, mark the first entry of every distinct column,
+ *      write the sorted source positions ("perm", 4 B / fat entry) and the number of distinct columns of the row
+ *   4. exclusive scan of the row lengths -> CSR row offsets; second sweep writes the column ids and the start of every
+ *      nonzero's run inside perm
+ *   5. values: nonzero k = elem_mats[perm[run]] summed left to right over its run — the same additions in the same
+ *      order as the host path.  Steps 1-4 depend on elem_rows only: with keep_plan the runs stay on the device and a
+ *      new set of element matrices costs one pass of step 5 (b200_mat_setvaluesbatch_values).
+ * Everything is HBM-bound integer work: per fat entry 4 B written + 4 B read of perm and 8 B of element matrix read. */
+#include "b200_internal.h"
+#include <vector>
+
+typedef unsigned long long u64;
+typedef unsigned int       u32;
+
+#define ASM_SENTINEL 0x7fffffffu      /* slot of the row's slice that holds no entry (negative column id)            */
+#define ASM_HEAD     0x80000000u      /* first entry of a run of equal columns                                        */
+#define ASM_WARP_CAP 512              /* fat entries a warp sorts in its shared-memory slab                           */
+#define ASM_CTA_CAP  4096             /* fat entries a CTA sorts in shared memory; longer rows sort in global scratch */
+#define ASM_WARPS    8
+#define ASM_FULL     0xffffffffu
+
+struct AsmStat { int bad_row, bad_col, nbig, maxfat; };
+
+struct BatchPlan {
+  long long nvals;                    /* ne*nl*nl: length of elem_mats                                                */
+  long long nfat;                     /* slots in perm                                                                */
+  long long nz;
+  u32      *d_perm;                   /* [nfat] source position in elem_mats | ASM_HEAD, rows in order, columns ascending */
+  int      *d_segoff;                 /* [nz+1] first slot of every nonzero's run                                     */
+};
+
+void b200_batchplan_free(void *plan)
+{
+  BatchPlan *P = (BatchPlan *)plan;
+  if (!P) return;
+  cudaFree(P->d_perm); cudaFree(P->d_segoff);
+  free(P);
+}
+
+namespace {
+struct DevBufs {                      /* temporaries of one assembly; whatever is still listed is freed on return     */
+  std::vector<void *> p;
+  ~DevBufs() { for (void *q : p) cudaFree(q); }
+  template <class T> cudaError_t get(T **out, size_t count)
+  {
+    void *q = NULL;
+    cudaError_t e = cudaMalloc(&q, sizeof(T) * (count ? count : 1));
+    if (e == cudaSuccess) p.push_back(q);
+    *out = (T *)q;
+    return e;
+  }
+  void release(void *q) { for (size_t k = 0; k < p.size(); k++) if (p[k] == q) { p.erase(p.begin() + k); return; } }
+};
+}
+
+/* ---- exclusive scan of n ints into out[0..n] (out[n] = total) ---------------------------------------------------- */
+#define SCAN_T 256
+#define SCAN_E 8
+
+__device__ __forceinline__ int cta_exclusive(int s, int *wsum, int *total)
+{
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  int inc = s;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(ASM_FULL, inc, d); if (lane >= d) inc += t; }
+  if (lane == 31) wsum[warp] = inc;
+  __syncthreads();
+  if (warp == 0) {
+    const int w = lane < nwarp ? wsum[lane] : 0;
+    int wi = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync(ASM_FULL, wi, d); if (lane >= d) wi += t; }
+    if (lane < nwarp) wsum[lane] = wi - w;
+    if (lane == 31) wsum[32] = wi;
+  }
+  __syncthreads();
+  const int excl = inc - s + wsum[warp];
+  *total = wsum[32];
+  __syncthreads();
+  return excl;
+}
+
+__global__ void __launch_bounds__(SCAN_T) scan_block_kernel(int n, const int *__restrict__ in, int *__restrict__ out, int *__restrict__ bsum)
+{
+  __shared__ int wsum[33];
+  const long long base = (long long)blockIdx.x * (SCAN_T * SCAN_E) + (long long)threadIdx.x * SCAN_E;
+  int v[SCAN_E], s = 0;
+#pragma unroll
+  for (int e = 0; e < SCAN_E; e++) { v[e] = base + e < n ? in[base + e] : 0; s += v[e]; }
+  int total;
+  int excl = cta_exclusive(s, wsum, &total);
+#pragma unroll
+  for (int e = 0; e < SCAN_E; e++) { if (base + e < n) out[base + e] = excl; excl += v[e]; }
+  if (threadIdx.x == 0) bsum[blockIdx.x] = total;
+}
+
+__global__ void __launch_bounds__(1024) scan_sums_kernel(int nb, int *bsum)
+{
+  __shared__ int wsum[33];
+  int carry = 0;
+  for (int base = 0; base < nb; base += 1024) {
+    const int idx = base + threadIdx.x;
+    const int v = idx < nb ? bsum[idx] : 0;
+    int total;
+    const int excl = cta_exclusive(v, wsum, &total);
+    if (idx < nb) bsum[idx] = carry + excl;
+    carry += total;
+  }
+  if (threadIdx.x == 0) bsum[nb] = carry;
+}
+
+__global__ void scan_add_kernel(int n, int *__restrict__ out, const int *__restrict__ bsum, int nb)
+{
+  for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (long long)gridDim.x * blockDim.x)
+    out[idx] += bsum[idx / (SCAN_T * SCAN_E)];
+  if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = bsum[nb];
+}
+
+static int dev_exclusive_scan(int n, const int *in, int *out, DevBufs &tmp, cudaStream_t st)
+{
+  const int nb = n > 0 ? (n + SCAN_T * SCAN_E - 1) / (SCAN_T * SCAN_E) : 0;
+  int *bsum;
+  B200_CUDA(tmp.get(&bsum, (size_t)nb + 1));
+  if (nb) { scan_block_kernel<<<nb, SCAN_T, 0, st>>>(n, in, out, bsum); B200_LAUNCHED(1); }
+  scan_sums_kernel<<<1, 1024, 0, st>>>(nb, bsum); B200_LAUNCHED(1);
+  int g = nb ? (n + 255) / 256 : 1;
+  if (g > B200_NSM * 16) g = B200_NSM * 16;
+  scan_add_kernel<<<g, 256, 0, st>>>(n, out, bsum, nb); B200_LAUNCHED(1);
+  return 0;
+}
+
+/* ---- steps 1, 2: occurrences of every row ------------------------------------------------------------------------- */
+__global__ void asm_count_kernel(long long nocc, const int *__restrict__ rows, int m, int *__restrict__ cnt, AsmStat *st)
+{
+  for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < nocc; o += (long long)gridDim.x * blockDim.x) {
+    const int r = rows[o];
+    if (r < 0) continue;                                   /* aij.c:311: negative rows are ignored */
+    if (r >= m) { atomicMax(&st->bad_row, r); continue; }
+    atomicAdd(&cnt[r], 1);
+  }
+}
+
+/* cnt counts down to zero while the slots fill from the back; the order inside a row is fixed later by the sort */
+__global__ void asm_fill_kernel(long long nocc, const int *__restrict__ rows, int m, const int *__restrict__ off, int *__restrict__ cnt, u32 *__restrict__ occ)
+{
+  for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < nocc; o += (long long)gridDim.x * blockDim.x) {
+    const int r = rows[o];
+    if (r < 0 || r >= m) continue;
+    const int pos = atomicSub(&cnt[r], 1) - 1;
+    occ[off[r] + pos] = (u32)o;
+  }
+}
+
+__global__ void asm_classify_kernel(int m, int nl, const int *__restrict__ off, int *__restrict__ big, AsmStat *st)
+{
+  for (long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x; r < m; r += (long long)gridDim.x * blockDim.x) {
+    const long long fat = (long long)(off[r + 1] - off[r]) * nl;
+    if (fat > ASM_WARP_CAP) {
+      big[atomicAdd(&st->nbig, 1)] = (int)r;
+      atomicMax(&st->maxfat, (int)fat);
+    }
+  }
+}
+
+/* ---- step 3: per-row sort ----------------------------------------------------------------------------------------- */
+template <bool WARP> __device__ __forceinline__ void grp_sync() { if (WARP) __syncwarp(); else __syncthreads(); }
+
+template <bool WARP>
+__device__ void bitonic_sort(u64 *k, int npad, int tid, int nt)
+{
+  for (int size = 2; size <= npad; size <<= 1)
+    for (int stride = size >> 1; stride > 0; stride >>= 1) {
+      for (int t = tid; t < (npad >> 1); t += nt) {
+        const int i = 2 * t - (t & (stride - 1));
+        const int j = i + stride;
+        const bool up = (i & size) == 0;
+        const u64 a = k[i], b = k[j];
+        if ((a > b) == up) { k[i] = b; k[j] = a; }
+      }
+      grp_sync<WARP>();
+    }
+}
+
+/* One row, by one warp (WARP) or one CTA.  keys: room for the padded number of fat entries.  Returns (to every thread
+ * of a warp; through *cta_heads for a CTA) the number of distinct columns. */
+template <bool WARP>
+__device__ void asm_sort_row(int r, int nl, int n, const int *__restrict__ off, u32 *occ, const int *__restrict__ rows,
+                             u64 *keys, u32 *__restrict__ perm, int *__restrict__ rowlen, AsmStat *st, int tid, int nt, int *cta_heads)
+{
+  const int o0 = off[r], c = off[r + 1] - o0;
+  if (c == 0) { if (tid == 0) rowlen[r] = 0; return; }
+  /* occurrences ascending = element order, then row-in-element order */
+  int cpad = 1;
+  while (cpad < c) cpad <<= 1;
+  for (int t = tid; t < cpad; t += nt) keys[t] = t < c ? (u64)occ[o0 + t] : ~0ull;
+  grp_sync<WARP>();
+  bitonic_sort<WARP>(keys, cpad, tid, nt);
+  for (int t = tid; t < c; t += nt) occ[o0 + t] = (u32)keys[t];
+  grp_sync<WARP>();
+  /* fat keys: (column, position in contribution order); skipped entries sort to the end */
+  const int L = c * nl;
+  int lpad = 1;
+  while (lpad < L) lpad <<= 1;
+  for (int p = tid; p < lpad; p += nt) {
+    u64 key = ~0ull;
+    if (p < L) {
+      const u32 o = occ[o0 + p / nl];
+      const int b = p % nl;
+      const int col = rows[(size_t)(o / (u32)nl) * nl + b];
+      if (col >= n) atomicMax(&st->bad_col, col);
+      else if (col >= 0) key = ((u64)(u32)col << 32) | (u32)p;   /* aij.c:325: negative columns are ignored */
+    }
+    keys[p] = key;
+  }
+  grp_sync<WARP>();
+  bitonic_sort<WARP>(keys, lpad, tid, nt);
+  int heads = 0;
+  const size_t f0 = (size_t)o0 * nl;
+  for (int q = tid; q < L; q += nt) {
+    const u64 key = keys[q];
+    u32 out = ASM_SENTINEL;
+    if (key != ~0ull) {
+      const u32 p = (u32)key;
+      const bool head = q == 0 || (u32)(keys[q - 1] >> 32) != (u32)(key >> 32);
+      out = (occ[o0 + p / nl] * (u32)nl + p % nl) | (head ? ASM_HEAD : 0u);
+      heads += head;
+    }
+    perm[f0 + q] = out;
+  }
+  if (WARP) {
+    heads = __reduce_add_sync(ASM_FULL, heads);
+    if (tid == 0) rowlen[r] = heads;
+    __syncwarp();
+  } else {
+    heads = __reduce_add_sync(ASM_FULL, heads);
+    if ((tid & 31) == 0 && heads) atomicAdd(cta_heads, heads);
+    __syncthreads();
+    if (tid == 0) { rowlen[r] = *cta_heads; *cta_heads = 0; }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(ASM_WARPS * 32) asm_sort_warp_kernel(int m, int nl, int n, const int *__restrict__ off, u32 *occ, const int *__restrict__ rows,
+                                                                        u32 *__restrict__ perm, int *__restrict__ rowlen, AsmStat *st)
+{
+  __shared__ u64 slab[ASM_WARPS][ASM_WARP_CAP];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (long long r = (long long)blockIdx.x * ASM_WARPS + warp; r < m; r += (long long)gridDim.x * ASM_WARPS) {
+    const long long fat = (long long)(off[r + 1] - off[r]) * nl;
+    if (fat > ASM_WARP_CAP) continue;                       /* the CTA kernel's rows */
+    asm_sort_row<true>((int)r, nl, n, off, occ, rows, slab[warp], perm, rowlen, st, lane, 32, NULL);
+  }
+}
+
+__global__ void __launch_bounds__(512) asm_sort_cta_kernel(int nbig, const int *__restrict__ big, int nl, int n, const int *__restrict__ off, u32 *occ, const int *__restrict__ rows,
+                                                          u32 *__restrict__ perm, int *__restrict__ rowlen, AsmStat *st, u64 *scratch, size_t scratch_per_cta)
+{
+  __shared__ u64 slab[ASM_CTA_CAP];
+  __shared__ int heads;
+  if (threadIdx.x == 0) heads = 0;
+  __syncthreads();
+  for (int b = blockIdx.x; b < nbig; b += gridDim.x) {
+    const int r = big[b];
+    const long long fat = (long long)(off[r + 1] - off[r]) * nl;
+    u64 *keys = fat <= ASM_CTA_CAP ? slab : scratch + (size_t)blockIdx.x * scratch_per_cta;
+    asm_sort_row<false>(r, nl, n, off, occ, rows, keys, perm, rowlen, st, threadIdx.x, blockDim.x, &heads);
+  }
+}
+
+/* ---- step 4: column ids and run starts ------------------------------------------------------------------------------ */
+__global__ void __launch_bounds__(256) asm_build_kernel(int m, int nl, const int *__restrict__ off, const u32 *__restrict__ perm, const int *__restrict__ ai,
+                                                        const int *__restrict__ rows, int *__restrict__ aj, int *__restrict__ segoff)
+{
+  const int lane = threadIdx.x & 31;
+  const long long gw = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5, nw = ((long long)gridDim.x * blockDim.x) >> 5;
+  for (long long r = gw; r < m; r += nw) {
+    const size_t f0 = (size_t)off[r] * nl;
+    const int L = (off[r + 1] - off[r]) * nl;
+    int base = ai[r];
+    for (int q0 = 0; q0 < L; q0 += 32) {
+      const int q = q0 + lane;
+      const u32 v = q < L ? perm[f0 + q] : ASM_SENTINEL;
+      const bool head = (v & ASM_HEAD) != 0;
+      const u32 ballot = __ballot_sync(ASM_FULL, head);
+      if (head) {
+        const int k = base + __popc(ballot & ((1u << lane) - 1u));
+        const u32 seq = v & ~ASM_HEAD;
+        const u32 o = seq / (u32)nl, b = seq % (u32)nl;
+        segoff[k] = (int)(f0 + q);
+        aj[k] = rows[(size_t)(o / (u32)nl) * nl + b];
+      }
+      base += __popc(ballot);
+    }
+  }
+  if (gw == 0 && lane == 0) segoff[ai[m]] = (int)((size_t)off[m] * nl);
+}
+
+/* ---- step 5: values = contributions summed in order ---------------------------------------------------------------- */
+__global__ void __launch_bounds__(256) asm_values_kernel(long long nz, const int *__restrict__ segoff, const u32 *__restrict__ perm, const double *__restrict__ em, double *__restrict__ a)
+{
+  for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nz; k += (long long)gridDim.x * blockDim.x) {
+    const int p0 = segoff[k], p1 = segoff[k + 1];
+    double s = em[perm[p0] & ~ASM_HEAD];                   /* a new nonzero starts as its first value (aij.c:350-366) */
+    for (int p = p0 + 1; p < p1; p++) {
+      const u32 v = perm[p];
+      if (v == ASM_SENTINEL) continue;                      /* tail of a row's slice (skipped columns), empty rows' slices */
+      s += em[v];
+    }
+    a[k] = s;
+  }
+}
+
+static int grid_for(long long n, int threads)
+{
+  long long g = (n + threads - 1) / threads;
+  if (g < 1) g = 1;
+  if (g > B200_NSM * 16) g = B200_NSM * 16;
+  return (int)g;
+}
+
+extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                                       int on_device, int keep_plan, b200_mat *A)
+{
+  B200_NEED_INIT();
+  if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
+  *A = NULL;
+  if (m < 0 || n < 0 || ne < 0 || nl < 1) return b200_seterr(B200_ERR_ARG_SIZ, "bad sizes m %d n %d elements %lld rows per element %d", m, n, ne, nl);
+  const long long nocc = ne * nl, nvals = nocc * nl;
+  if (nvals >= 0x7fffffffLL) return b200_seterr(B200_ERR_ARG_SIZ, "element matrices hold %lld values; the limit is 2^31 - 2 per matrix", nvals);
+  if (ne > 0 && (!elem_rows || !elem_mats)) return b200_seterr(B200_ERR_ARG_NULL, "null element arrays");
+  cudaStream_t st = g_b200.stream;
+  DevBufs tmp;
+  const int *d_rows = elem_rows;
+  const double *d_em = elem_mats;
+  if (!on_device) {
+    int *r; double *v;
+    B200_CUDA(tmp.get(&r, (size_t)nocc));
+    B200_CUDA(tmp.get(&v, (size_t)nvals));
+    if (ne) {
+      B200_CUDA(cudaMemcpyAsync(r, elem_rows, sizeof(int) * (size_t)nocc, cudaMemcpyHostToDevice, st));
+      B200_CUDA(cudaMemcpyAsync(v, elem_mats, sizeof(double) * (size_t)nvals, cudaMemcpyHostToDevice, st));
+    }
+    d_rows = r; d_em = v;
+  }
+  int *cnt, *off, *rowlen, *ai, *big;
+  u32 *occ, *perm;
+  AsmStat *dstat, hstat = {-1, -1, 0, 0};
+  B200_CUDA(tmp.get(&cnt, (size_t)m + 1));
+  B200_CUDA(tmp.get(&off, (size_t)m + 1));
+  B200_CUDA(tmp.get(&rowlen, (size_t)m + 1));
+  B200_CUDA(tmp.get(&ai, (size_t)m + 1));
+  B200_CUDA(tmp.get(&occ, (size_t)nocc));
+  B200_CUDA(tmp.get(&perm, (size_t)nvals));
+  B200_CUDA(tmp.get(&big, (size_t)(nvals / ASM_WARP_CAP) + 1));
+  B200_CUDA(tmp.get(&dstat, 1));
+  B200_CUDA(cudaMemcpyAsync(dstat, &hstat, sizeof(hstat), cudaMemcpyHostToDevice, st));
+  B200_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)m + 1), st));
+  /* 1, 2: occurrence lists */
+  asm_count_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, m, cnt, dstat); B200_LAUNCHED(1);
+  B200_CHK(dev_exclusive_scan(m, cnt, off, tmp, st));
+  asm_fill_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, m, off, cnt, occ); B200_LAUNCHED(1);
+  asm_classify_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, nl, off, big, dstat); B200_LAUNCHED(1);
+  B200_CUDA(cudaMemcpyAsync(&hstat, dstat, sizeof(hstat), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  if (hstat.bad_row >= 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Row too large: row %d max %d", hstat.bad_row, m - 1);
+  /* 3: per-row sort */
+  asm_sort_warp_kernel<<<grid_for(m, ASM_WARPS), ASM_WARPS * 32, 0, st>>>(m, nl, n, off, occ, d_rows, perm, rowlen, dstat); B200_LAUNCHED(1);
+  if (hstat.nbig) {
+    int g = hstat.nbig < B200_NSM * 2 ? hstat.nbig : B200_NSM * 2;
+    u64 *scratch = NULL;
+    size_t per = 0;
+    if (hstat.maxfat > ASM_CTA_CAP) {
+      per = 1;
+      while (per < (size_t)hstat.maxfat) per <<= 1;
+      if (g > B200_NSM) g = B200_NSM;
+      B200_CUDA(tmp.get(&scratch, per * (size_t)g));
+    }
+    asm_sort_cta_kernel<<<g, 512, 0, st>>>(hstat.nbig, big, nl, n, off, occ, d_rows, perm, rowlen, dstat, scratch, per); B200_LAUNCHED(1);
+  }
+  /* 4: row offsets, column ids, run starts */
+  B200_CHK(dev_exclusive_scan(m, rowlen, ai, tmp, st));
+  std::vector<int> hi((size_t)m + 1);
+  B200_CUDA(cudaMemcpyAsync(hi.data(), ai, sizeof(int) * ((size_t)m + 1), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaMemcpyAsync(&hstat, dstat, sizeof(hstat), cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  if (hstat.bad_col >= 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Column too large: col %d max %d", hstat.bad_col, n - 1);
+  const long long nz = hi[m];
+  int *d_j, *segoff;
+  double *d_a;
+  B200_CUDA(tmp.get(&d_j, (size_t)nz + 8));
+  B200_CUDA(tmp.get(&d_a, (size_t)nz + 8));
+  B200_CUDA(tmp.get(&segoff, (size_t)nz + 1));
+  asm_build_kernel<<<grid_for(m, 8), 256, 0, st>>>(m, nl, off, perm, ai, d_rows, d_j, segoff); B200_LAUNCHED(1);
+  /* 5: values */
+  if (nz) { asm_values_kernel<<<grid_for(nz, 256), 256, 0, st>>>(nz, segoff, perm, d_em, d_a); B200_LAUNCHED(1); }
+  B200_CUDA(cudaStreamSynchronize(st));
+
+  b200_mat M = (b200_mat)calloc(1, sizeof(*M));
+  if (!M) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  M->kind = 0;
+  tmp.release(d_j); tmp.release(d_a);                       /* adopted by the block, also when the call below fails */
+  int rc = b200_seq_adopt(&M->A, m, n, hi.data(), d_j, d_a);
+  if (rc) { b200_seq_free(&M->A); free(M); return rc; }
+  if (keep_plan) {
+    BatchPlan *P = (BatchPlan *)calloc(1, sizeof(*P));
+    if (!P) { b200_mat_destroy(M); return b200_seterr(B200_ERR_MEM, "out of host memory"); }
+    P->nvals = nvals; P->nfat = nvals; P->nz = nz; P->d_perm = perm; P->d_segoff = segoff;
+    tmp.release(perm); tmp.release(segoff);
+    M->batchplan = P;
+  }
+  *A = M;
+  return 0;
+}
+
+extern "C" int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mats, int on_device)
+{
+  B200_NEED_INIT();
+  if (!A || !elem_mats) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  BatchPlan *P = (BatchPlan *)A->batchplan;
+  if (A->kind != 0 || !P) return b200_seterr(B200_ERR_ARG_WRONGSTATE, "matrix was not built by b200_mat_setvaluesbatch with keep_plan");
+  cudaStream_t st = g_b200.stream;
+  DevBufs tmp;
+  const double *d_em = elem_mats;
+  if (!on_device) {
+    double *v;
+    B200_CUDA(tmp.get(&v, (size_t)P->nvals));
+    B200_CUDA(cudaMemcpyAsync(v, elem_mats, sizeof(double) * (size_t)P->nvals, cudaMemcpyHostToDevice, st));
+    d_em = v;
+  }
+  if (A->A.T) { b200_seq_free(A->A.T); free(A->A.T); A->A.T = NULL; }        /* rebuilt from the new values on demand */
+  if (P->nz) { asm_values_kernel<<<grid_for(P->nz, 256), 256, 0, st>>>(P->nz, P->d_segoff, P->d_perm, d_em, A->A.d_a); B200_LAUNCHED(1); }
+  if (!on_device) B200_CUDA(cudaStreamSynchronize(st));    /* the staging copy is freed on return */
+  return 0;
+}
+
+extern "C" int b200_mat_get_csr(b200_mat A, int *i, int *j, double *a)
+{
+  B200_NEED_INIT();
+  if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null matrix");
+  if (A->kind != 0 || A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "CSR read-back is for sequential, unstripped matrices");
+  cudaStream_t st = g_b200.stream;
+  const B200Seq *S = &A->A;
+  if (i) B200_CUDA(cudaMemcpyAsync(i, S->d_i, sizeof(int) * ((size_t)S->m + 1), cudaMemcpyDeviceToHost, st));
+  if (j && S->nz) B200_CUDA(cudaMemcpyAsync(j, S->d_j, sizeof(int) * (size_t)S->nz, cudaMemcpyDeviceToHost, st));
+  if (a && S->nz) B200_CUDA(cudaMemcpyAsync(a, S->d_a, sizeof(double) * (size_t)S->nz, cudaMemcpyDeviceToHost, st));
+  B200_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}

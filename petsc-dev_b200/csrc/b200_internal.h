@@ -105,9 +105,11 @@ struct b200_mat_s {
   long long repoch;           /* reverse-exchange counter (MatMultTranspose)                                          */
   double  *d_ghost_t;         /* [nghost] B^T x, what this rank contributes to rows its neighbours own                */
   void    *peerplan;          /* per-matrix peer-store plan (b200_comm.cu)                                            */
+  void    *batchplan;         /* element -> nonzero plan kept by the device assembly (b200_assembly.cu), or NULL       */
 };
 
 int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
+int  b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_j, double *d_a);
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
 int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);
@@ -122,6 +124,7 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x);
 int b200_mpiaij_exchange_end(b200_mat A);
 int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, double *z);   /* yin NULL: plain transpose product */
 void b200_mpiaij_peer_free(b200_mat A);
+void b200_batchplan_free(void *plan);
 bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox);
 
 /* reduction grid helper */

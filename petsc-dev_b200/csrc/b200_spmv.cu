@@ -97,14 +97,17 @@ void b200_seq_free(B200Seq *S)
   memset(S, 0, sizeof(*S));
 }
 
-static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a)
+/* i is a host array.  j / a are host arrays that are copied, unless adopt: then they are device arrays of nz + 8
+ * entries (cudaMalloc'ed by the caller, e.g. the device assembly) whose ownership passes to S. */
+static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a, bool adopt = false)
 {
   memset(S, 0, sizeof(*S));
+  if (adopt) { S->d_j = const_cast<int *>(j); S->d_a = const_cast<double *>(a); }   /* owned from here on, also on failure */
   if (m < 0 || n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative matrix size %d x %d", m, n);
   if (!i || i[0] != 0) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets must start at 0");
   const long long nz = i[m];
   if (nz < 0) return b200_seterr(B200_ERR_ARG_WRONG, "negative nonzero count");
-  if (nz > 0 && (!j || !a)) return b200_seterr(B200_ERR_ARG_NULL, "null column/value arrays");
+  if ((nz > 0 || adopt) && (!j || !a)) return b200_seterr(B200_ERR_ARG_NULL, "null column/value arrays");
   S->m = m; S->n = n; S->nz = nz; S->req_G = g_tune_G;
   /* row statistics + the visiting order */
   int nonempty = 0;
@@ -186,12 +189,14 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
 
   const size_t pad = 8;
   B200_CUDA(cudaMalloc((void **)&S->d_i, sizeof(int) * ((size_t)m + 1)));
-  B200_CUDA(cudaMalloc((void **)&S->d_j, sizeof(int) * ((size_t)nz + pad)));
-  B200_CUDA(cudaMalloc((void **)&S->d_a, sizeof(double) * ((size_t)nz + pad)));
   B200_CUDA(cudaMemcpy(S->d_i, i, sizeof(int) * ((size_t)m + 1), cudaMemcpyHostToDevice));
-  if (nz) {
-    B200_CUDA(cudaMemcpy(S->d_j, j, sizeof(int) * (size_t)nz, cudaMemcpyHostToDevice));
-    B200_CUDA(cudaMemcpy(S->d_a, a, sizeof(double) * (size_t)nz, cudaMemcpyHostToDevice));
+  if (!adopt) {
+    B200_CUDA(cudaMalloc((void **)&S->d_j, sizeof(int) * ((size_t)nz + pad)));
+    B200_CUDA(cudaMalloc((void **)&S->d_a, sizeof(double) * ((size_t)nz + pad)));
+    if (nz) {
+      B200_CUDA(cudaMemcpy(S->d_j, j, sizeof(int) * (size_t)nz, cudaMemcpyHostToDevice));
+      B200_CUDA(cudaMemcpy(S->d_a, a, sizeof(double) * (size_t)nz, cudaMemcpyHostToDevice));
+    }
   }
   B200_CUDA(cudaMemset(S->d_j + nz, 0, sizeof(int) * pad));
   B200_CUDA(cudaMemset(S->d_a + nz, 0, sizeof(double) * pad));
@@ -286,6 +291,14 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
   for (int k = 0; k < ns; k++) { S->ntiles += S->strips[k].ntiles; S->nlong += S->strips[k].nlong; }
   S->ncrows = m;
   return 0;
+}
+
+/* Block from a CSR whose column ids and values already live on the device (device assembly, b200_assembly.cu): only
+ * the row offsets pass through the host (the row binning is computed from them); d_j / d_a (nz + 8 entries each) are
+ * adopted.  Column strips are not formed on this path. */
+int b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_j, double *d_a)
+{
+  return seq_upload_one(S, m, n, i_host, d_j, d_a, true);
 }
 
 extern "C" int b200_spmv_set_strips(int nstrips)
@@ -672,6 +685,7 @@ extern "C" int b200_mat_destroy(b200_mat A)
   if (!A) return 0;
   if (g_b200.inited) cudaStreamSynchronize(g_b200.stream);
   b200_seq_free(&A->A);
+  if (A->batchplan) b200_batchplan_free(A->batchplan);
   if (A->kind) {
     b200_seq_free(&A->B);
     if (A->peerplan) b200_mpiaij_peer_free(A);

@@ -184,3 +184,35 @@ def split_ownership(N, size, bs=1):
     nb = N // bs
     n = np.array([nb // size + (1 if (nb % size) > r else 0) for r in range(size)], dtype=np.int64) * bs
     return np.concatenate([[0], np.cumsum(n)])
+
+
+# ---- element batches for MatSetValuesBatch (src/mat/interface/matrix.c:1698) ---------------------------------------
+def elements_tri2d(X, Y):
+    """The mesh of src/ksp/ksp/examples/tutorials/ex4.c:46-111 on an X x Y vertex grid: every cell is cut into two
+    triangles with the element matrix [[1, -.5, -.5], [-.5, .5, 0], [-.5, 0, .5]] (explicit zeros included).
+    Returns (N, nl, elem_rows int32[ne*3], elem_mats float64[ne*9])."""
+    j, i = np.meshgrid(np.arange(Y - 1), np.arange(X - 1), indexing="ij")
+    a = (j * X + i).reshape(-1)
+    b, c, d = a + 1, a + X, a + X + 1
+    rows = np.stack([a, b, c, d, c, b], axis=1).astype(np.int32).reshape(-1)      # lower (A,B,C) then upper (D,C,B)
+    em = np.array([1.0, -0.5, -0.5, -0.5, 0.5, 0.0, -0.5, 0.0, 0.5])
+    mats = np.tile(em, 2 * a.size)
+    return X * Y, 3, rows, mats
+
+
+def elements_hex3d(nx, seed=11, scale_values=True):
+    """Q1 hexahedra on an nx^3 vertex grid (nl = 8): a fixed symmetric 8 x 8 pattern matrix times a per-element
+    coefficient hashed from the element id, so the contributions that meet in a nonzero all differ (the summation
+    order matters for the last bit).  Returns (N, nl, elem_rows, elem_mats)."""
+    ne1 = nx - 1
+    k, j, i = np.meshgrid(np.arange(ne1), np.arange(ne1), np.arange(ne1), indexing="ij")
+    v0 = ((k * nx + j) * nx + i).reshape(-1).astype(np.int64)
+    corner = np.array([0, 1, nx, nx + 1, nx * nx, nx * nx + 1, nx * nx + nx, nx * nx + nx + 1], dtype=np.int64)
+    rows = (v0[:, None] + corner[None, :]).astype(np.int32).reshape(-1)
+    d = np.abs(np.arange(8)[:, None] ^ np.arange(8)[None, :])
+    hamming = (d & 1) + ((d >> 1) & 1) + ((d >> 2) & 1)
+    base = np.array([4.0, 0.0, -1.0, -1.0])[hamming] / 3.0                          # Laplacian-like: row sums are 0
+    ne = v0.size
+    coef = 0.5 + u01(hash3(seed, np.arange(ne, dtype=np.uint64), 7)) if scale_values else np.ones(ne)
+    mats = (coef[:, None] * base.reshape(1, 64)).reshape(-1)
+    return nx ** 3, 8, rows, mats

@@ -6,6 +6,7 @@
       src/ksp/ksp/examples/tutorials/output/ex2_1.out     GMRES residual history of ex2 -m 5 -n 5 (refine_always)
       src/ksp/ksp/examples/tutorials/output/ex5_1.out     GMRES+Jacobi history of ex5 (first solve)
       src/ksp/pc/examples/tests/output/ex2_1.out          CG + PCNONE history on the 10x10 tridiagonal matrix
+      src/ksp/ksp/examples/tutorials/output/ex4_0.out     MatSetValuesBatch: the matrix assembled from ex4's 8 triangles
   oracle_fixtures.npz     outputs of the reference library itself (oracle/_ref, built by oracle/build_ref.py) on
       seeded inputs: Vec kernels, MatMult/MatMultAdd, CG and GMRES residual histories.  The GPU tests compare
       against these even where the oracle .so is absent.
@@ -67,6 +68,18 @@ def main():
                       "history": monitor_norms(os.path.join(REF, "src/ksp/ksp/examples/tutorials/output/ex5_1.out"))}
     g["pc_ex2_1"] = {"source": "src/ksp/pc/examples/tests/output/ex2_1.out",
                      "history": monitor_norms(os.path.join(REF, "src/ksp/pc/examples/tests/output/ex2_1.out"))}
+    # MatSetValuesBatch: the assembled 9 x 9 matrix the reference's DEVICE assembly printed (first MatView of ex4_0.out,
+    # "type: seqaijcusp"): 41 entries, explicit zeros kept
+    ex4 = os.path.join(REF, "src/ksp/ksp/examples/tutorials/output/ex4_0.out")
+    lines = open(ex4).read().splitlines()
+    k = next(i for i, l in enumerate(lines) if l.strip() == "type: seqaijcusp")
+    rows = []
+    for l in lines[k + 1:]:
+        m = re.match(r"row (\d+):(.*)$", l)
+        if not m:
+            break
+        rows.append([[int(c), float(v)] for c, v in re.findall(r"\((\d+), ([-+0-9.eE]+)\)", m.group(2))])
+    g["ksp_ex4_0"] = {"source": "src/ksp/ksp/examples/tutorials/output/ex4_0.out", "grid": [3, 3], "rows": rows}
     json.dump(g, open(os.path.join(HERE, "reference_goldens.json"), "w"), indent=1)
 
     # ---- oracle outputs on seeded inputs ----
@@ -106,6 +119,10 @@ def main():
     b = A.mult(np.ones(3000))
     r = A.ksp_solve(b, "gmres", "jacobi", rtol=1e-8)
     fx["plaw3000_gmres_hist"] = r["history"]; fx["plaw3000_gmres_its"] = np.array(r["its"])
+    # MatSetValuesBatch through the reference's host path (one MatSetValues/ADD_VALUES per element)
+    Nh, nl, er, em = P.elements_hex3d(6)
+    hi, hj, ha = R.mat_setvaluesbatch(Nh, Nh, er, em, nl).csr()
+    fx["hex6_batch_i"], fx["hex6_batch_j"], fx["hex6_batch_a"] = hi, hj, ha
     np.savez_compressed(os.path.join(HERE, "oracle_fixtures.npz"), **fx)
     print("wrote", len(g), "reference goldens and", len(fx), "oracle fixtures")
 
