@@ -21,9 +21,12 @@
  *   5. values: nonzero k = elem_mats[perm[run]] summed left to right over its run — the same additions in the same
  *      order as the host path.  Steps 1-4 depend on elem_rows only: with keep_plan the runs stay on the device and a
  *      new set of element matrices costs one pass of step 5 (b200_mat_setvaluesbatch_values).
- * Everything is HBM-bound integer work: per fat entry 4 B written + 4 B read of perm and 8 B of element matrix read. */
+ * Step 5 is HBM-bound: 8 B (value) + 4 B (perm) per fat entry, 4 B (run start) + 8 B (result) per nonzero. */
 #include "b200_internal.h"
 #include <vector>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 
 typedef unsigned long long u64;
 typedef unsigned int       u32;
@@ -54,18 +57,52 @@ void b200_batchplan_free(void *plan)
 }
 
 namespace {
-struct DevBufs {                      /* temporaries of one assembly; whatever is still listed is freed on return     */
-  std::vector<void *> p;
-  ~DevBufs() { for (void *q : p) cudaFree(q); }
-  template <class T> cudaError_t get(T **out, size_t count)
+/* Temporaries of one assembly; whatever is still listed is released on return.  Stream-ordered allocations from the
+ * device's default pool (its release threshold is raised to 8 GiB once, so after the first assembly they cost microseconds;
+ * plain cudaMalloc/cudaFree of these half-gigabyte buffers was most of the wall time).  Buffers that outlive the call
+ * (column ids, values, the kept plan) are plain cudaMalloc'ed: get(..., true). */
+struct DevBufs {
+  struct Item { void *p; bool pooled; };
+  std::vector<Item> items;
+  cudaStream_t st;
+  explicit DevBufs(cudaStream_t s) : st(s)
+  {
+    static bool pool_ready = false;
+    if (!pool_ready) {
+      int dev = 0;
+      cudaMemPool_t pool;
+      if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        unsigned long long keep = 8ull << 30;             /* the pool may hold on to 8 GiB between assemblies */
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+      pool_ready = true;
+    }
+  }
+  ~DevBufs() { for (Item &q : items) { if (q.pooled) cudaFreeAsync(q.p, st); else cudaFree(q.p); } }
+  template <class T> cudaError_t get(T **out, size_t count, bool persistent = false)
   {
     void *q = NULL;
-    cudaError_t e = cudaMalloc(&q, sizeof(T) * (count ? count : 1));
-    if (e == cudaSuccess) p.push_back(q);
+    const size_t bytes = sizeof(T) * (count ? count : 1);
+    cudaError_t e = persistent ? cudaMalloc(&q, bytes) : cudaMallocAsync(&q, bytes, st);
+    if (e == cudaSuccess) items.push_back({q, !persistent});
     *out = (T *)q;
     return e;
   }
-  void release(void *q) { for (size_t k = 0; k < p.size(); k++) if (p[k] == q) { p.erase(p.begin() + k); return; } }
+  void release(void *q) { for (size_t k = 0; k < items.size(); k++) if (items[k].p == q) { items.erase(items.begin() + k); return; } }
+};
+
+struct AsmTrace {                     /* B200_ASM_TRACE=1: wall-clock milliseconds of the phases on stderr */
+  bool on;
+  std::chrono::steady_clock::time_point t0;
+  AsmTrace() : on(getenv("B200_ASM_TRACE") != NULL), t0(std::chrono::steady_clock::now()) {}
+  void mark(const char *what)
+  {
+    if (!on) return;
+    cudaDeviceSynchronize();
+    auto t1 = std::chrono::steady_clock::now();
+    fprintf(stderr, "[b200 assembly] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+    t0 = t1;
+  }
 };
 }
 
@@ -215,6 +252,7 @@ __device__ void asm_sort_row(int r, int nl, int n, const int *__restrict__ off, 
   grp_sync<WARP>();
   /* fat keys: (column, position in contribution order); skipped entries sort to the end */
   const int L = c * nl;
+  const size_t f0 = (size_t)o0 * nl;
   int lpad = 1;
   while (lpad < L) lpad <<= 1;
   for (int p = tid; p < lpad; p += nt) {
@@ -231,7 +269,6 @@ __device__ void asm_sort_row(int r, int nl, int n, const int *__restrict__ off, 
   grp_sync<WARP>();
   bitonic_sort<WARP>(keys, lpad, tid, nt);
   int heads = 0;
-  const size_t f0 = (size_t)o0 * nl;
   for (int q = tid; q < L; q += nt) {
     const u64 key = keys[q];
     u32 out = ASM_SENTINEL;
@@ -312,15 +349,29 @@ __global__ void __launch_bounds__(256) asm_build_kernel(int m, int nl, const int
 }
 
 /* ---- step 5: values = contributions summed in order ---------------------------------------------------------------- */
+/* Nonzero k = its run of perm, summed in slot order.  The first ASM_VAL_UNROLL slots of the run are loaded together
+ * (all index loads, then all value loads in flight), the additions stay in slot order; slots past the run or holding
+ * the sentinel (tail of a row's slice) add nothing.
+ * Tried and dropped: one warp per row reading the element values in their own order (whole sectors) and dropping them
+ * into sorted slots in shared memory through an inverse map — same bytes, but the per-row latency chain left the
+ * SMs idle: 1.31 ms against 0.49 ms for this kernel on the 128^3 hexahedral mesh. */
+#define ASM_VAL_UNROLL 8
 __global__ void __launch_bounds__(256) asm_values_kernel(long long nz, const int *__restrict__ segoff, const u32 *__restrict__ perm, const double *__restrict__ em, double *__restrict__ a)
 {
   for (long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x; k < nz; k += (long long)gridDim.x * blockDim.x) {
     const int p0 = segoff[k], p1 = segoff[k + 1];
-    double s = em[perm[p0] & ~ASM_HEAD];                   /* a new nonzero starts as its first value (aij.c:350-366) */
-    for (int p = p0 + 1; p < p1; p++) {
-      const u32 v = perm[p];
-      if (v == ASM_SENTINEL) continue;                      /* tail of a row's slice (skipped columns), empty rows' slices */
-      s += em[v];
+    u32 idx[ASM_VAL_UNROLL];
+    double v[ASM_VAL_UNROLL];
+#pragma unroll
+    for (int t = 0; t < ASM_VAL_UNROLL; t++) idx[t] = p0 + t < p1 ? (__ldcs(perm + p0 + t) & ~ASM_HEAD) : ASM_SENTINEL;
+#pragma unroll
+    for (int t = 0; t < ASM_VAL_UNROLL; t++) v[t] = idx[t] != ASM_SENTINEL ? __ldcs(em + idx[t]) : 0.0;
+    double s = v[0];                                        /* a new nonzero starts as its first value (aij.c:350-366) */
+#pragma unroll
+    for (int t = 1; t < ASM_VAL_UNROLL; t++) if (idx[t] != ASM_SENTINEL) s += v[t];
+    for (int p = p0 + ASM_VAL_UNROLL; p < p1; p++) {
+      const u32 i = perm[p];
+      if (i != ASM_SENTINEL) s += em[i];
     }
     a[k] = s;
   }
@@ -345,7 +396,8 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   if (nvals >= 0x7fffffffLL) return b200_seterr(B200_ERR_ARG_SIZ, "element matrices hold %lld values; the limit is 2^31 - 2 per matrix", nvals);
   if (ne > 0 && (!elem_rows || !elem_mats)) return b200_seterr(B200_ERR_ARG_NULL, "null element arrays");
   cudaStream_t st = g_b200.stream;
-  DevBufs tmp;
+  DevBufs tmp(st);
+  AsmTrace trace;
   const int *d_rows = elem_rows;
   const double *d_em = elem_mats;
   if (!on_device) {
@@ -362,13 +414,15 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   u32 *occ, *perm;
   AsmStat *dstat, hstat = {-1, -1, 0, 0};
   B200_CUDA(tmp.get(&cnt, (size_t)m + 1));
+  const bool keep = keep_plan != 0;
   B200_CUDA(tmp.get(&off, (size_t)m + 1));
   B200_CUDA(tmp.get(&rowlen, (size_t)m + 1));
   B200_CUDA(tmp.get(&ai, (size_t)m + 1));
   B200_CUDA(tmp.get(&occ, (size_t)nocc));
-  B200_CUDA(tmp.get(&perm, (size_t)nvals));
+  B200_CUDA(tmp.get(&perm, (size_t)nvals, keep));
   B200_CUDA(tmp.get(&big, (size_t)(nvals / ASM_WARP_CAP) + 1));
   B200_CUDA(tmp.get(&dstat, 1));
+  trace.mark("allocations");
   B200_CUDA(cudaMemcpyAsync(dstat, &hstat, sizeof(hstat), cudaMemcpyHostToDevice, st));
   B200_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)m + 1), st));
   /* 1, 2: occurrence lists */
@@ -379,6 +433,7 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   B200_CUDA(cudaMemcpyAsync(&hstat, dstat, sizeof(hstat), cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
   if (hstat.bad_row >= 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Row too large: row %d max %d", hstat.bad_row, m - 1);
+  trace.mark("occurrence lists");
   /* 3: per-row sort */
   asm_sort_warp_kernel<<<grid_for(m, ASM_WARPS), ASM_WARPS * 32, 0, st>>>(m, nl, n, off, occ, d_rows, perm, rowlen, dstat); B200_LAUNCHED(1);
   if (hstat.nbig) {
@@ -393,6 +448,7 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
     }
     asm_sort_cta_kernel<<<g, 512, 0, st>>>(hstat.nbig, big, nl, n, off, occ, d_rows, perm, rowlen, dstat, scratch, per); B200_LAUNCHED(1);
   }
+  trace.mark("per-row sort");
   /* 4: row offsets, column ids, run starts */
   B200_CHK(dev_exclusive_scan(m, rowlen, ai, tmp, st));
   std::vector<int> hi((size_t)m + 1);
@@ -403,13 +459,15 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   const long long nz = hi[m];
   int *d_j, *segoff;
   double *d_a;
-  B200_CUDA(tmp.get(&d_j, (size_t)nz + 8));
-  B200_CUDA(tmp.get(&d_a, (size_t)nz + 8));
-  B200_CUDA(tmp.get(&segoff, (size_t)nz + 1));
+  trace.mark("row offsets to host");
+  B200_CUDA(tmp.get(&d_j, (size_t)nz + 8, true));
+  B200_CUDA(tmp.get(&d_a, (size_t)nz + 8, true));
+  B200_CUDA(tmp.get(&segoff, (size_t)nz + 1, keep));
   asm_build_kernel<<<grid_for(m, 8), 256, 0, st>>>(m, nl, off, perm, ai, d_rows, d_j, segoff); B200_LAUNCHED(1);
   /* 5: values */
   if (nz) { asm_values_kernel<<<grid_for(nz, 256), 256, 0, st>>>(nz, segoff, perm, d_em, d_a); B200_LAUNCHED(1); }
   B200_CUDA(cudaStreamSynchronize(st));
+  trace.mark("column ids + values");
 
   b200_mat M = (b200_mat)calloc(1, sizeof(*M));
   if (!M) return b200_seterr(B200_ERR_MEM, "out of host memory");
@@ -417,6 +475,7 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   tmp.release(d_j); tmp.release(d_a);                       /* adopted by the block, also when the call below fails */
   int rc = b200_seq_adopt(&M->A, m, n, hi.data(), d_j, d_a);
   if (rc) { b200_seq_free(&M->A); free(M); return rc; }
+  trace.mark("row binning (host)");
   if (keep_plan) {
     BatchPlan *P = (BatchPlan *)calloc(1, sizeof(*P));
     if (!P) { b200_mat_destroy(M); return b200_seterr(B200_ERR_MEM, "out of host memory"); }
@@ -435,7 +494,7 @@ extern "C" int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mat
   BatchPlan *P = (BatchPlan *)A->batchplan;
   if (A->kind != 0 || !P) return b200_seterr(B200_ERR_ARG_WRONGSTATE, "matrix was not built by b200_mat_setvaluesbatch with keep_plan");
   cudaStream_t st = g_b200.stream;
-  DevBufs tmp;
+  DevBufs tmp(st);
   const double *d_em = elem_mats;
   if (!on_device) {
     double *v;

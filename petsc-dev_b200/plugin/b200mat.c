@@ -3,7 +3,8 @@
  * Mirrors MatCreate_SeqAIJCUSP (reference src/mat/impls/aij/seq/seqcusp/aijcusp.cu:657-681) and MatCreate_MPIAIJCUSP
  * (src/mat/impls/aij/mpi/mpicusp/mpiaijcusp.cu:192-226): inherit the complete host CSR type (MatCreate_SeqAIJ aij.c:3886,
  * MatCreate_MPIAIJ mpiaij.c:5617 — preallocation, MatSetValues, assembly, views, MatGetDiagonal ... all stay host code),
- * override mult / multadd / multtranspose / multtransposeadd / getvecs / destroy, switch the inode path off (aijcusp.cu:665).
+ * override mult / multadd / multtranspose / multtransposeadd / getvecs / destroy (+ setvaluesbatch for the sequential
+ * type, aijcusp.cu:639), switch the inode path off (aijcusp.cu:665).
  *
  * Device copy: built lazily at the first MatMult after the matrix changed.  "Changed" is detected with the object state
  * every mutating Mat front end bumps (MatAssemblyEnd, MatScale, MatShift, MatZeroEntries, MatDiagonalScale, MatZeroRows:
@@ -170,6 +171,40 @@ static PetscErrorCode MatGetVecs_SeqAIJB200(Mat mat,Vec *right,Vec *left)       
   PetscFunctionReturn(0);
 }
 
+/* MatSetValuesBatch_SeqAIJCUSP (src/mat/impls/aij/seq/seqcusp/aijAssemble.cu:157-290): the element matrices are
+ * assembled on the device (b200_mat_setvaluesbatch: per-row sort + ordered sums, bit-identical to the host loop of
+ * matrix.c:1712-1716 on an empty matrix); like the reference's version it "creates the given matrix" — whatever
+ * preallocated pattern J had is replaced — and the host copy is filled from the device result (the reference's
+ * MatCUSPCopyFromGPU step, aijAssemble.cu:287).  The device matrix stays: the next MatMult only refreshes values. */
+#undef __FUNCT__
+#define __FUNCT__ "MatSetValuesBatch_SeqAIJB200"
+static PetscErrorCode MatSetValuesBatch_SeqAIJB200(Mat J,PetscInt Ne,PetscInt Nl,PetscInt *elemRows,const PetscScalar *elemMats)
+{
+  Mat_SeqAIJB200 *d = (Mat_SeqAIJB200*)J->spptr;
+  PetscInt       m = J->rmap->n,n = J->cmap->n,*ci,*cj;
+  PetscScalar    *ca;
+  long long      nz;
+  b200_mat       dm;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = PetscInfo3(J,"Assembling %D element matrices of %D x %D on the device\n",Ne,Nl,Nl);CHKERRQ(ierr);
+  CHKB200(b200_mat_setvaluesbatch(m,n,(long long)Ne,Nl,elemRows,elemMats,0,0,&dm));
+  CHKB200(b200_mat_get_size(dm,0,0,&nz));
+  ierr = PetscMalloc3(m+1,PetscInt,&ci,(size_t)nz+1,PetscInt,&cj,(size_t)nz+1,PetscScalar,&ca);CHKERRQ(ierr);
+  CHKB200(b200_mat_get_csr(dm,ci,cj,ca));
+  ierr = MatSeqAIJSetPreallocationCSR(J,ci,cj,ca);CHKERRQ(ierr);                  /* sorted rows: straight copies, then assembles */
+  if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); }
+  ierr = PetscFree(d->i);CHKERRQ(ierr);
+  d->mat = dm; d->m = m; d->nz = (PetscInt)nz;
+  ierr = PetscMalloc((m+1)*sizeof(PetscInt),&d->i);CHKERRQ(ierr);
+  ierr = PetscMemcpy(d->i,ci,(m+1)*sizeof(PetscInt));CHKERRQ(ierr);
+  d->state = ((PetscObject)J)->state;
+  PetscB200MatUploads++;
+  ierr = PetscFree3(ci,cj,ca);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
 #undef __FUNCT__
 #define __FUNCT__ "MatDestroy_SeqAIJB200"
 static PetscErrorCode MatDestroy_SeqAIJB200(Mat A)                                /* MatDestroy_SeqAIJCUSP aijcusp.cu:566 */
@@ -207,6 +242,7 @@ PetscErrorCode MatCreate_SeqAIJB200(Mat B)
   B->ops->multtransposeadd = MatMultTransposeAdd_SeqAIJB200;
   B->ops->getvecs = MatGetVecs_SeqAIJB200;
   B->ops->destroy = MatDestroy_SeqAIJB200;
+  B->ops->setvaluesbatch = MatSetValuesBatch_SeqAIJB200;                          /* aijcusp.cu:639 */
   ierr = PetscObjectChangeTypeName((PetscObject)B,MATSEQAIJB200);CHKERRQ(ierr);
   PetscFunctionReturn(0);
 }
