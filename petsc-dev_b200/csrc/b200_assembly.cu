@@ -57,13 +57,13 @@ void b200_batchplan_free(void *plan)
 }
 
 namespace {
-/* Temporaries of one assembly; whatever is still listed is released on return.  Stream-ordered allocations from the
- * device's default pool (its release threshold is raised to 8 GiB once, so after the first assembly they cost microseconds;
- * plain cudaMalloc/cudaFree of these half-gigabyte buffers was most of the wall time).  Buffers that outlive the call
- * (column ids, values, the kept plan) are plain cudaMalloc'ed: get(..., true). */
+/* Device buffers of one assembly; whatever is still listed is released on return, what the matrix keeps (column ids,
+ * values, the kept plan) is taken off the list with release().  Everything is a stream-ordered allocation from the
+ * device's default pool, whose release threshold is raised to 8 GiB once: after the first assembly an allocation costs
+ * microseconds (plain cudaMalloc/cudaFree of these half-gigabyte buffers was 2/3 of the wall time).  The kept buffers
+ * are later freed with cudaFree, which accepts pool allocations and hands them back to the pool. */
 struct DevBufs {
-  struct Item { void *p; bool pooled; };
-  std::vector<Item> items;
+  std::vector<void *> items;
   cudaStream_t st;
   explicit DevBufs(cudaStream_t s) : st(s)
   {
@@ -72,23 +72,22 @@ struct DevBufs {
       int dev = 0;
       cudaMemPool_t pool;
       if (cudaGetDevice(&dev) == cudaSuccess && cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
-        unsigned long long keep = 8ull << 30;             /* the pool may hold on to 8 GiB between assemblies */
+        unsigned long long keep = 8ull << 30;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
       }
       pool_ready = true;
     }
   }
-  ~DevBufs() { for (Item &q : items) { if (q.pooled) cudaFreeAsync(q.p, st); else cudaFree(q.p); } }
-  template <class T> cudaError_t get(T **out, size_t count, bool persistent = false)
+  ~DevBufs() { for (void *q : items) cudaFreeAsync(q, st); }
+  template <class T> cudaError_t get(T **out, size_t count)
   {
     void *q = NULL;
-    const size_t bytes = sizeof(T) * (count ? count : 1);
-    cudaError_t e = persistent ? cudaMalloc(&q, bytes) : cudaMallocAsync(&q, bytes, st);
-    if (e == cudaSuccess) items.push_back({q, !persistent});
+    cudaError_t e = cudaMallocAsync(&q, sizeof(T) * (count ? count : 1), st);
+    if (e == cudaSuccess) items.push_back(q);
     *out = (T *)q;
     return e;
   }
-  void release(void *q) { for (size_t k = 0; k < items.size(); k++) if (items[k].p == q) { items.erase(items.begin() + k); return; } }
+  void release(void *q) { for (size_t k = 0; k < items.size(); k++) if (items[k] == q) { items.erase(items.begin() + k); return; } }
 };
 
 struct AsmTrace {                     /* B200_ASM_TRACE=1: wall-clock milliseconds of the phases on stderr */
@@ -414,12 +413,11 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   u32 *occ, *perm;
   AsmStat *dstat, hstat = {-1, -1, 0, 0};
   B200_CUDA(tmp.get(&cnt, (size_t)m + 1));
-  const bool keep = keep_plan != 0;
   B200_CUDA(tmp.get(&off, (size_t)m + 1));
   B200_CUDA(tmp.get(&rowlen, (size_t)m + 1));
   B200_CUDA(tmp.get(&ai, (size_t)m + 1));
   B200_CUDA(tmp.get(&occ, (size_t)nocc));
-  B200_CUDA(tmp.get(&perm, (size_t)nvals, keep));
+  B200_CUDA(tmp.get(&perm, (size_t)nvals));
   B200_CUDA(tmp.get(&big, (size_t)(nvals / ASM_WARP_CAP) + 1));
   B200_CUDA(tmp.get(&dstat, 1));
   trace.mark("allocations");
@@ -460,9 +458,9 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   int *d_j, *segoff;
   double *d_a;
   trace.mark("row offsets to host");
-  B200_CUDA(tmp.get(&d_j, (size_t)nz + 8, true));
-  B200_CUDA(tmp.get(&d_a, (size_t)nz + 8, true));
-  B200_CUDA(tmp.get(&segoff, (size_t)nz + 1, keep));
+  B200_CUDA(tmp.get(&d_j, (size_t)nz + 8));
+  B200_CUDA(tmp.get(&d_a, (size_t)nz + 8));
+  B200_CUDA(tmp.get(&segoff, (size_t)nz + 1));
   asm_build_kernel<<<grid_for(m, 8), 256, 0, st>>>(m, nl, off, perm, ai, d_rows, d_j, segoff); B200_LAUNCHED(1);
   /* 5: values */
   if (nz) { asm_values_kernel<<<grid_for(nz, 256), 256, 0, st>>>(nz, segoff, perm, d_em, d_a); B200_LAUNCHED(1); }

@@ -16,6 +16,7 @@
  */
 #include "b200_internal.h"
 #include <vector>
+#include <algorithm>
 #include <math.h>
 
 #include "b200_spmv_kernels.cuh"
@@ -110,10 +111,19 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   if ((nz > 0 || adopt) && (!j || !a)) return b200_seterr(B200_ERR_ARG_NULL, "null column/value arrays");
   S->m = m; S->n = n; S->nz = nz; S->req_G = g_tune_G;
   /* row statistics + the visiting order */
-  int nonempty = 0;
+  /* one pass: validity, non-empty rows, longest row, sum of squared lengths (integer accumulators: a floating-point
+   * running sum makes this loop latency-bound, and it runs at every upload) */
+  int nonempty = 0, maxlen = 0, bad = 0;
+  unsigned long long sumsq = 0;
   for (int r = 0; r < m; r++) {
-    if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
-    nonempty += (i[r + 1] > i[r]);
+    const int l = i[r + 1] - i[r];
+    bad |= l;                                              /* sign bit set <=> some length negative */
+    nonempty += (l > 0);
+    maxlen = l > maxlen ? l : maxlen;
+    sumsq += (unsigned long long)((long long)l * l);
+  }
+  if (bad < 0) {
+    for (int r = 0; r < m; r++) if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
   }
   S->nonzerorow = nonempty;
   /* compressed-row rule: reference uses it when the fraction of EMPTY rows exceeds 0.6 (aij.c:818,859) */
@@ -138,8 +148,14 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
     S->cfg = cfg;
     /* statistics of the non-empty rows: mean and coefficient of variation of the lengths */
     const double mean = nonempty ? (double)nz / (double)nonempty : 0.0;
-    double ss = 0.0;
-    for (int r = 0; r < m; r++) { const double l = (double)(i[r + 1] - i[r]); if (l > 0) ss += (l - mean) * (l - mean); }
+    double ss;
+    if (maxlen <= (1 << 26)) {
+      ss = (double)sumsq - (double)nonempty * mean * mean;  /* sum (l - mean)^2 over the non-empty rows; sumsq <= nz * maxlen < 2^57 */
+      if (ss < 0.0) ss = 0.0;
+    } else {                                                /* gigantic rows: the integer sum could wrap */
+      ss = 0.0;
+      for (int r = 0; r < m; r++) { const double l = (double)(i[r + 1] - i[r]); if (l > 0) ss += (l - mean) * (l - mean); }
+    }
     const double cv = (nonempty && mean > 0) ? sqrt(ss / (double)nonempty) / mean : 0.0;
     /* lanes per row: one lane (reference summation order) up to 32 entries per row, else about 8-16 entries per lane */
     int G = 1;
@@ -164,6 +180,20 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   std::vector<int>  longrows, longstart;
   int ts = 0, nchunks = 0;
   auto close_tile = [&](int re) { if (re > ts) tiles.push_back(make_int4(ts, re, vi[ts], vi[re])); };
+  if (maxlen <= S->long_thresh) {
+    /* no long rows: the greedy packing below reduces to "as many rows as fit", found per tile by a bounded binary
+     * search instead of a walk over every row (same tiles) */
+    tiles.reserve((size_t)(nz / tile_nnz) + (size_t)(nrows / tile_rows) + 2);
+    while (ts < nrows) {
+      const int hi = ts + tile_rows < nrows ? ts + tile_rows : nrows;
+      int re = hi;
+      if (vi[hi] - vi[ts] > tile_nnz)
+        re = (int)(std::upper_bound(vi + ts + 1, vi + hi + 1, (long long)vi[ts] + tile_nnz, [](long long v, int e) { return v < (long long)e; }) - vi) - 1;
+      if (re <= ts) re = ts + 1;                            /* cannot happen (a row is at most long_thresh <= tile_nnz long) */
+      close_tile(re);
+      ts = re;
+    }
+  } else
   for (int r = 0; r < nrows; r++) {
     const int len = vi[r + 1] - vi[r];
     if (len > S->long_thresh) {
@@ -258,10 +288,19 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
   S->strip_nzoff = (long long *)calloc((size_t)ns + 1, sizeof(long long));
   if (!S->strips || !S->strip_nzoff) return b200_seterr(B200_ERR_MEM, "out of host memory");
   const int width = (int)(((long long)n + ns - 1) / ns);
-  int nonempty = 0;
+  /* one pass: validity, non-empty rows, longest row, sum of squared lengths (integer accumulators: a floating-point
+   * running sum makes this loop latency-bound, and it runs at every upload) */
+  int nonempty = 0, maxlen = 0, bad = 0;
+  unsigned long long sumsq = 0;
   for (int r = 0; r < m; r++) {
-    if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
-    nonempty += (i[r + 1] > i[r]);
+    const int l = i[r + 1] - i[r];
+    bad |= l;                                              /* sign bit set <=> some length negative */
+    nonempty += (l > 0);
+    maxlen = l > maxlen ? l : maxlen;
+    sumsq += (unsigned long long)((long long)l * l);
+  }
+  if (bad < 0) {
+    for (int r = 0; r < m; r++) if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
   }
   S->nonzerorow = nonempty;
   std::vector<int> si((size_t)m + 1), sj;
