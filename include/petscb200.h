@@ -140,6 +140,9 @@ int b200_vec_dotnorm2(int n, const double *s, const double *t, double *dp_host, 
  * (src/mat/impls/aij/seq/seqcusp/aijcusp.cu:126,458).  The host arrays are not retained. */
 int b200_mat_create_seqaij(int m, int n, const int *i_host, const int *j_host, const double *a_host, b200_mat *A);
 int b200_mat_update_values(b200_mat A, const double *a_host);    /* same pattern, new values (value-only re-upload) */
+/* The same for the parallel type: new values of the diagonal and of the off-diagonal block (Mat_MPIAIJ::A, ::B in their
+ * assembled order), pattern, ghost columns and exchange plan unchanged — nothing collective happens. */
+int b200_mat_update_values_mpiaij(b200_mat A, const double *a_diag_host, const double *a_offdiag_host);
 /* Device assembly: MatSetValuesBatch (src/mat/interface/matrix.c:1698; the reference's device version is
  * MatSetValuesBatch_SeqAIJCUSP, src/mat/impls/aij/seq/seqcusp/aijAssemble.cu:157-290).  ne element matrices of nl x nl
  * values (row-major, concatenated in elem_mats) are added into the rows/columns elem_rows[e*nl .. e*nl+nl) of a new

@@ -275,6 +275,11 @@ class Mat:
         aa = _f64(aa)
         _chk(lib.b200_mat_update_values(self.h, _dp(aa)), "MatAssemblyEnd (values)")
 
+    def update_values_mpiaij(self, a_diag, a_offdiag):
+        """Parallel type: new values of both blocks, same pattern and exchange plan (nothing collective)."""
+        ad, ao = _f64(a_diag), _f64(a_offdiag)
+        _chk(lib.b200_mat_update_values_mpiaij(self.h, _dp(ad), _dp(ao)), "MatAssemblyEnd_MPIAIJ (values)")
+
     @classmethod
     def set_values_batch(cls, m, n, nl, elem_rows, elem_mats, keep_plan=False):
         """MatSetValuesBatch (matrix.c:1698) on the device: ne element matrices of nl x nl values added into the rows and

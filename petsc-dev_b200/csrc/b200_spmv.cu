@@ -540,6 +540,23 @@ extern "C" int b200_mat_update_values(b200_mat A, const double *a)
   return 0;
 }
 
+extern "C" int b200_mat_update_values_mpiaij(b200_mat A, const double *ad, const double *ao)
+{
+  B200_NEED_INIT();
+  if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null matrix");
+  if (A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not a parallel matrix");
+  if ((A->A.nz && !ad) || (A->B.nz && !ao)) return b200_seterr(B200_ERR_ARG_NULL, "null value array");
+  if (A->A.nstrips > 1 || A->B.nstrips > 1) return b200_seterr(B200_ERR_SUP, "value refresh is not implemented for a column-stripped block (recreate the matrix)");
+  B200Seq *blk[2] = {&A->A, &A->B};
+  const double *src[2] = {ad, ao};
+  for (int k = 0; k < 2; k++) {
+    if (blk[k]->T) { b200_seq_free(blk[k]->T); free(blk[k]->T); blk[k]->T = NULL; }   /* rebuilt from the new values on demand */
+    if (blk[k]->nz) B200_CUDA(cudaMemcpyAsync(blk[k]->d_a, src[k], sizeof(double) * (size_t)blk[k]->nz, cudaMemcpyHostToDevice, g_b200.stream));
+  }
+  B200_CUDA(cudaStreamSynchronize(g_b200.stream));
+  return 0;
+}
+
 extern "C" int b200_mat_get_size(b200_mat A, int *m, int *n, long long *nz)
 {
   if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null matrix");

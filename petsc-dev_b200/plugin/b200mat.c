@@ -9,8 +9,10 @@
  * Device copy: built lazily at the first MatMult after the matrix changed.  "Changed" is detected with the object state
  * every mutating Mat front end bumps (MatAssemblyEnd, MatScale, MatShift, MatZeroEntries, MatDiagonalScale, MatZeroRows:
  * PetscObjectStateIncrease in src/mat/interface/matrix.c) — the PETSC_HAVE_CUSP build marks the same places with
- * valid_GPU_matrix = PETSC_CUSP_CPU (matrix.c:1085-1089,4917-4921).  When the row offsets are unchanged only the values
- * are re-sent (b200_mat_update_values), not the whole matrix as MatCUSPCopyToGPU does (aijcusp.cu:138-152). */
+ * valid_GPU_matrix = PETSC_CUSP_CPU (matrix.c:1085-1089,4917-4921).  When the row offsets (and, for the parallel type, the
+ * ghost columns) are unchanged only the values are re-sent (b200_mat_update_values[_mpiaij]) — no re-binning, no new
+ * exchange plan — not the whole matrix as MatCUSPCopyToGPU does (aijcusp.cu:138-152); a new preallocation drops the
+ * device copy, because it can keep the row lengths and change the columns. */
 #include "petscb200plugin.h"
 #include <../src/mat/impls/aij/seq/aij.h>
 #include <../src/mat/impls/aij/mpi/mpiaij.h>
@@ -31,6 +33,8 @@ typedef struct {
 typedef struct {
   b200_mat  mat;          /* diagonal block, off-diagonal block, ghost plan     */
   PetscInt  state,stateA,stateB;
+  PetscInt  m,nzA,nzB,nghost;
+  PetscInt *iA,*iB,*garray; /* host copies of what was uploaded: row offsets of both blocks, ghost columns */
 } Mat_MPIAIJB200;
 
 /* ------------------------------------------------------------------------------------------------ sequential */
@@ -53,6 +57,7 @@ static PetscErrorCode MatB200CopyToDevice_SeqAIJ(Mat A)                         
   if (same) {
     CHKB200(b200_mat_update_values(d->mat,a->a));
     PetscB200MatValueUpdates++;
+    ierr = PetscInfo1(A,"B200 device copy: values refreshed (%D nonzeros), pattern unchanged\n",a->nz);CHKERRQ(ierr);
   } else {
     if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }
     ierr = PetscFree(d->i);CHKERRQ(ierr);
@@ -61,6 +66,7 @@ static PetscErrorCode MatB200CopyToDevice_SeqAIJ(Mat A)                         
     ierr = PetscMemcpy(d->i,a->i,(m+1)*sizeof(PetscInt));CHKERRQ(ierr);
     d->m = m; d->nz = a->nz;
     PetscB200MatUploads++;
+    ierr = PetscInfo1(A,"B200 device copy: full upload (%D nonzeros)\n",a->nz);CHKERRQ(ierr);
   }
   d->state = ((PetscObject)A)->state;
   PetscFunctionReturn(0);
@@ -171,6 +177,24 @@ static PetscErrorCode MatGetVecs_SeqAIJB200(Mat mat,Vec *right,Vec *left)       
   PetscFunctionReturn(0);
 }
 
+/* The values-only refresh above trusts "same row offsets => same pattern".  That holds for everything that edits an
+ * assembled matrix (a new nonzero lengthens its row), but NOT for a second preallocation, which throws the arrays away
+ * and may be followed by different columns with the same row lengths.  So preallocation drops the device copy. */
+EXTERN_C_BEGIN
+#undef __FUNCT__
+#define __FUNCT__ "MatSeqAIJSetPreallocation_SeqAIJB200"
+PetscErrorCode MatSeqAIJSetPreallocation_SeqAIJB200(Mat B,PetscInt nz,const PetscInt *nnz)
+{
+  Mat_SeqAIJB200 *d = (Mat_SeqAIJB200*)B->spptr;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  if (d && d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }
+  ierr = MatSeqAIJSetPreallocation_SeqAIJ(B,nz,nnz);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+EXTERN_C_END
+
 /* MatSetValuesBatch_SeqAIJCUSP (src/mat/impls/aij/seq/seqcusp/aijAssemble.cu:157-290): the element matrices are
  * assembled on the device (b200_mat_setvaluesbatch: per-row sort + ordered sums, bit-identical to the host loop of
  * matrix.c:1712-1716 on an empty matrix); like the reference's version it "creates the given matrix" — whatever
@@ -243,6 +267,8 @@ PetscErrorCode MatCreate_SeqAIJB200(Mat B)
   B->ops->getvecs = MatGetVecs_SeqAIJB200;
   B->ops->destroy = MatDestroy_SeqAIJB200;
   B->ops->setvaluesbatch = MatSetValuesBatch_SeqAIJB200;                          /* aijcusp.cu:639 */
+  ierr = PetscObjectComposeFunctionDynamic((PetscObject)B,"MatSeqAIJSetPreallocation_C","MatSeqAIJSetPreallocation_SeqAIJB200",
+                                           MatSeqAIJSetPreallocation_SeqAIJB200);CHKERRQ(ierr);
   ierr = PetscObjectChangeTypeName((PetscObject)B,MATSEQAIJB200);CHKERRQ(ierr);
   PetscFunctionReturn(0);
 }
@@ -254,9 +280,11 @@ EXTERN_C_END
 static PetscErrorCode MatMPIAIJSetPreallocation_MPIAIJB200(Mat B,PetscInt d_nz,const PetscInt d_nnz[],PetscInt o_nz,const PetscInt o_nnz[])
 {                                                                                 /* mpiaijcusp.cu:9-55 */
   Mat_MPIAIJ     *b = (Mat_MPIAIJ*)B->data;
+  Mat_MPIAIJB200 *d = (Mat_MPIAIJB200*)b->spptr;
   PetscErrorCode ierr;
 
   PetscFunctionBegin;
+  if (d && d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }              /* a new preallocation may keep the row lengths and change the columns */
   if (!B->preallocated) {
     /* the two sequential blocks are of our type, so every host op on them stays coherent with the device copy */
     ierr = PetscLayoutSetUp(B->rmap);CHKERRQ(ierr);
@@ -289,11 +317,40 @@ static PetscErrorCode MatB200CopyToDevice_MPIAIJ(Mat A)
   Mat_SeqAIJ     *ad = (Mat_SeqAIJ*)a->A->data,*ao = (Mat_SeqAIJ*)a->B->data;
   PetscInt       nghost = a->B->cmap->n,nto = 0,nfrom = 0,i,k,c;
   int            *to_procs = 0,*to_starts = 0,*to_indices = 0,*from_procs = 0,*from_starts = 0;
+  PetscBool      same = PETSC_FALSE;
   PetscErrorCode ierr;
 
   PetscFunctionBegin;
   if (!A->assembled) SETERRQ(((PetscObject)A)->comm,PETSC_ERR_ARG_WRONGSTATE,"Not for unassembled matrix");
   if (d->mat && d->state == ((PetscObject)A)->state && d->stateA == ((PetscObject)a->A)->state && d->stateB == ((PetscObject)a->B)->state) PetscFunctionReturn(0);
+  if (d->mat && d->m == A->rmap->n && d->nzA == ad->nz && d->nzB == ao->nz && d->nghost == nghost) {
+    /* same row offsets in both blocks and the same ghost columns: the pattern, the exchange plan and the peer buffers
+     * stand, only the values travel (MatAssemblyEnd_MPIAIJ rebuilds B and garray whenever a new off-process column
+     * appears, mpiaij.c:696-710, which changes these arrays).  The decision must be the same on every rank: a full
+     * rebuild is collective. */
+    PetscBool sA,sB,sG = PETSC_TRUE;
+    ierr = PetscMemcmp(d->iA,ad->i,(d->m+1)*sizeof(PetscInt),&sA);CHKERRQ(ierr);
+    ierr = PetscMemcmp(d->iB,ao->i,(d->m+1)*sizeof(PetscInt),&sB);CHKERRQ(ierr);
+    if (nghost) { ierr = PetscMemcmp(d->garray,a->garray,nghost*sizeof(PetscInt),&sG);CHKERRQ(ierr); }
+    same = (PetscBool)(sA && sB && sG);
+    if (same) {                                                                   /* column-stripped blocks are not refreshed in place */
+      int sa = 1,sb = 1;
+      CHKB200(b200_mat_strips(d->mat,&sa,&sb));
+      if (sa > 1 || sb > 1) same = PETSC_FALSE;
+    }
+  }
+  {
+    PetscInt mine = same ? 1 : 0,all = mine;
+    if (a->size > 1) { ierr = MPI_Allreduce(&mine,&all,1,MPIU_INT,MPI_MIN,((PetscObject)A)->comm);CHKERRQ(ierr); }
+    same = all ? PETSC_TRUE : PETSC_FALSE;
+  }
+  if (same) {
+    CHKB200(b200_mat_update_values_mpiaij(d->mat,ad->a,ao->a));
+    PetscB200MatValueUpdates++;
+    ierr = PetscInfo2(A,"B200 device copy: values refreshed (%D + %D nonzeros), pattern and ghost exchange unchanged\n",ad->nz,ao->nz);CHKERRQ(ierr);
+    d->state = ((PetscObject)A)->state; d->stateA = ((PetscObject)a->A)->state; d->stateB = ((PetscObject)a->B)->state;
+    PetscFunctionReturn(0);
+  }
   if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); d->mat = 0; }
   if (a->size > 1) {
     VecScatter_MPI_General *to = (VecScatter_MPI_General*)a->Mvctx->todata,*from = (VecScatter_MPI_General*)a->Mvctx->fromdata;
@@ -313,6 +370,13 @@ static PetscErrorCode MatB200CopyToDevice_MPIAIJ(Mat A)
                                  nto,to_procs,to_starts,to_indices,nfrom,from_procs,from_starts,&d->mat));
   if (a->size > 1) { ierr = PetscFree5(to_procs,to_starts,to_indices,from_procs,from_starts);CHKERRQ(ierr); }
   PetscB200MatUploads++;
+  ierr = PetscInfo2(A,"B200 device copy: full upload (%D + %D nonzeros) and ghost exchange plan\n",ad->nz,ao->nz);CHKERRQ(ierr);
+  ierr = PetscFree3(d->iA,d->iB,d->garray);CHKERRQ(ierr);
+  d->m = A->rmap->n; d->nzA = ad->nz; d->nzB = ao->nz; d->nghost = nghost;
+  ierr = PetscMalloc3(d->m+1,PetscInt,&d->iA,d->m+1,PetscInt,&d->iB,nghost+1,PetscInt,&d->garray);CHKERRQ(ierr);
+  ierr = PetscMemcpy(d->iA,ad->i,(d->m+1)*sizeof(PetscInt));CHKERRQ(ierr);
+  ierr = PetscMemcpy(d->iB,ao->i,(d->m+1)*sizeof(PetscInt));CHKERRQ(ierr);
+  if (nghost) { ierr = PetscMemcpy(d->garray,a->garray,nghost*sizeof(PetscInt));CHKERRQ(ierr); }
   d->state = ((PetscObject)A)->state; d->stateA = ((PetscObject)a->A)->state; d->stateB = ((PetscObject)a->B)->state;
   PetscFunctionReturn(0);
 }
@@ -443,6 +507,7 @@ static PetscErrorCode MatDestroy_MPIAIJB200(Mat A)                              
   PetscFunctionBegin;
   if (d) {
     if (d->mat) { CHKB200(b200_mat_destroy(d->mat)); }
+    ierr = PetscFree3(d->iA,d->iB,d->garray);CHKERRQ(ierr);
     ierr = PetscFree(d);CHKERRQ(ierr);
     a->spptr = 0;
   }

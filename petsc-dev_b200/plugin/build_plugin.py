@@ -24,6 +24,7 @@ BINDIR = os.path.join(REFLIBDIR, "bin")
 EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
     "ksp_ex2": "src/ksp/ksp/examples/tutorials/ex2.c",
     "ksp_ex4": "src/ksp/ksp/examples/tutorials/ex4.c",
+    "ksp_ex5": "src/ksp/ksp/examples/tutorials/ex5.c",
     "mat_ex5": "src/mat/examples/tests/ex5.c",
     "vec_tut_ex1": "src/vec/vec/examples/tutorials/ex1.c",
     "vec_ex43": "src/vec/vec/examples/tests/ex43.c",

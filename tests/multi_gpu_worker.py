@@ -55,6 +55,16 @@ def main():
             A = par.create_mpiaij(host)
         finally:
             pb.spmv_tuning()
+        # same pattern, new values (b200_mat_update_values_mpiaij): away and back again; everything below then runs
+        # on the refreshed operator, and the doubled one must give exactly twice the product
+        sp = host["split"]
+        xh0 = P.random_vector(N, 2)
+        x0, z0, z1 = pb.Vec(re_ - rs, xh0[rs:re_]), pb.Vec(re_ - rs), pb.Vec(re_ - rs)
+        A.mult(x0, z0)
+        A.update_values_mpiaij(2.0 * np.asarray(sp["Aa"]), 2.0 * np.asarray(sp["Ba"]))
+        A.mult(x0, z1)
+        refresh_ok = bool(np.array_equal(z1.get_array(), 2.0 * z0.get_array()))
+        A.update_values_mpiaij(sp["Aa"], sp["Ba"])
         xh, yh = P.random_vector(N, 2), P.random_vector(N, 3)
         x, y, z = pb.Vec(m, xh[rs:re_]), pb.Vec(m, yh[rs:re_]), pb.Vec(m)
 
@@ -90,6 +100,9 @@ def main():
                 r = pb.ksp_solve(A, b, sol, ksp_type=kt, pc_type="jacobi", rtol=1e-8, fused=fused, check_every=1)
                 ksp["%s_%d" % (kt, fused)] = dict(its=int(r["its"]), reason=int(r["reason"]), history=[float(v) for v in r["history"]],
                                                   sol=gather(sol).tolist() if N <= 5000 else None)
+        rk = torch.tensor([1.0 if refresh_ok else 0.0], device="cuda")
+        dist.all_reduce(rk, op=dist.ReduceOp.MIN)
+        refresh_ok = bool(rk.item() == 1.0)
         if rank == 0:
             def gen0(r0, r1):
                 a_i, a_j, a_a = gen(r0, r1)
@@ -117,6 +130,7 @@ def main():
                 res["multadd_ok"] = bool(np.array_equal(got_add, want_add))
                 res["bit_exact"] = True
             res["max_abs_err"] = float(np.max(np.abs(got - want)))
+            res["refresh_ok"] = refresh_ok
             res["dot_rel"] = float(abs(dot - R.vec_dot(xh, yh)) / abs(R.vec_dot(xh, yh)))
             res["norm_rel"] = float(abs(nrm - R.vec_norm(xh)) / R.vec_norm(xh))
             if ksp:

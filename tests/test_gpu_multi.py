@@ -43,6 +43,7 @@ def test_mpiaij_across_gpus(world, transport):
     for name, res in out["cases"].items():
         assert res["mult_ok"] and res["multadd_ok"], (name, res)          # bit-exact for the stencils, 1e-12 for plaw
         assert res["multtranspose_ok"], (name, res)                        # reverse exchange with ADD_VALUES
+        assert res["refresh_ok"], (name, res)                              # value-only refresh of both blocks, every rank
         assert res["dot_rel"] < 1e-13 and res["norm_rel"] < 1e-13, (name, res)
         for key in ("cg_0", "cg_1", "gmres_0"):
             if key in res:

@@ -128,3 +128,14 @@ def test_ex4_matsetvaluesbatch_on_device():
     hg, hw = history(got), history(ref)
     assert len(hg) == len(hw) and len(hg) > 5, (len(hg), len(hw))
     assert max(abs(a - b) / b for a, b in zip(hg, hw)) <= 1e-10
+
+
+@pytest.mark.parametrize("case,uploads", [("ksp_ex5_1", "SeqAIJ"), ("ksp_ex5_mpiaij", "MPIAIJ")])
+def test_same_pattern_reassembly_refreshes_values_only(case, uploads):
+    """ex5 assembles a second matrix with the same nonzero structure: one full upload, then values only (-info lines of
+    MatB200CopyToDevice_*); a MatSeqAIJSetPreallocation in between would have dropped the device copy instead."""
+    c = CASES[case]
+    out = run(c["prog"], c["args"] + ["-dll_prepend", PLUGIN] + c["b200_args"] + ["-info"])
+    mine = [l for l in out.splitlines() if "MatB200CopyToDevice_%s" % uploads in l]
+    assert sum("full upload" in l for l in mine) == 1, mine
+    assert sum("values refreshed" in l for l in mine) >= 1, mine
