@@ -261,6 +261,8 @@ typedef struct {
   double gmres_haptol;       /* default 1e-30                                                                    */
   int    fused;              /* 0 = op-by-op exactly like the reference's call sequence; 1 = fused kernels       */
   int    check_every;        /* fused CG only: host looks at the device-side convergence flag every k iterations */
+  int    gmres_modified_gs;  /* 1 = modified Gram-Schmidt (borthog.c:30-52: one VecDot + VecAXPY per basis vector)
+                                instead of the default classical one (borthog2.c:35-118); -ksp_gmres_modifiedgramschmidt */
 } b200_ksp_options;
 int b200_ksp_default_options(b200_ksp_options *o);
 typedef struct {

@@ -254,7 +254,7 @@ class KSPOptions(C.Structure):
     _fields_ = [("ksp_type", C.c_int), ("pc_type", C.c_int), ("rtol", C.c_double), ("abstol", C.c_double),
                 ("dtol", C.c_double), ("max_it", C.c_int), ("norm_type", C.c_int), ("guess_nonzero", C.c_int),
                 ("gmres_restart", C.c_int), ("gmres_cgs_refine", C.c_int), ("gmres_haptol", C.c_double),
-                ("fused", C.c_int), ("check_every", C.c_int)]
+                ("fused", C.c_int), ("check_every", C.c_int), ("gmres_modified_gs", C.c_int)]
 
 
 class Mat:
@@ -404,7 +404,7 @@ def ksp_options(**kw):
 def ksp_solve(A, b, x, histmax=None, **kw):
     """KSPSolve(ksp, b, x): returns dict(its, reason, history, rnorm, solve_ms).  Keyword options are the fields of
     b200_ksp_options (ksp_type='cg'|'gmres', pc_type='jacobi'|'none', rtol, abstol, dtol, max_it, norm_type,
-    guess_nonzero, gmres_restart, gmres_cgs_refine, fused, check_every)."""
+    guess_nonzero, gmres_restart, gmres_cgs_refine, gmres_modified_gs, fused, check_every)."""
     o = ksp_options(**kw)
     histmax = (o.max_it + 2) if histmax is None else int(histmax)
     hist = np.zeros(max(histmax, 1))

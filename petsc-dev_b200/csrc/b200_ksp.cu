@@ -646,8 +646,16 @@ static int gmres_solve(b200_mat A, const Pc *pc, Conv *cv, const b200_ksp_option
       /* KSP_PCApplyBAorAB, left: VV(it+1) = B A VV(it) */
       if ((rc = op_mult(A, VV(it), MATOP))) break;
       if ((rc = pc_apply(pc, MATOP, VV(it + 1)))) break;
-      /* classical Gram-Schmidt (borthog2.c:52-82) */
       double *hh = g.HH(0, it), *hes = g.HES(0, it), *lhh = g.lhh.data();
+      if (o->gmres_modified_gs) {
+        /* modified Gram-Schmidt (borthog.c:41-49): hh[j] = (vv(it+1), vv(j)); vv(it+1) -= hh[j] vv(j), one j at a time */
+        for (int j = 0; j <= it; j++) {
+          if ((rc = b200_vec_dot(n, VV(it + 1), vv[j], &hh[j]))) break;
+          hes[j] = hh[j];
+          if ((rc = b200_vec_axpy(n, VV(it + 1), -hh[j], vv[j]))) break;
+        }
+      } else {
+      /* classical Gram-Schmidt (borthog2.c:52-82) */
       for (int j = 0; j <= it; j++) { hh[j] = 0.0; hes[j] = 0.0; }
       bool refine = (o->gmres_cgs_refine == 2);
       for (int pass = 0; pass < 2; pass++) {
@@ -663,6 +671,7 @@ static int gmres_solve(b200_mat A, const Pc *pc, Conv *cv, const b200_ksp_option
           if (wnrm < 1.0286 * hnrm) refine = true;
         }
         if (!refine) break;
+      }
       }
       if (rc) break;
       if ((rc = vec_normalize(n, VV(it + 1), &tt))) break;
@@ -724,6 +733,7 @@ extern "C" int b200_ksp_default_options(b200_ksp_options *o)
   o->norm_type = B200_KSP_NORM_PRECONDITIONED;
   o->guess_nonzero = 0;
   o->gmres_restart = 30; o->gmres_cgs_refine = 0; o->gmres_haptol = 1e-30; /* gmres.c:947-956 */
+  o->gmres_modified_gs = 0;
   o->fused = 1; o->check_every = 16;
   return 0;
 }

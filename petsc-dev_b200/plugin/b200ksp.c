@@ -21,6 +21,8 @@ typedef struct {
   PetscInt  restart;           /* -ksp_gmres_restart                             */
   PetscInt  check_every;       /* -ksp_b200_check_every: host looks at the device-side convergence flag every k iterations */
   PetscBool fused;             /* -ksp_b200_fused 0: the reference's op-by-op call sequence on the device                  */
+  PetscBool mgs;               /* -ksp_gmres_modifiedgramschmidt (gmres.c:534)                                            */
+  KSPGMRESCGSRefinementType refine; /* -ksp_gmres_cgs_refinement_type (gmres.c:529)                                          */
 } KSP_B200;
 
 #undef __FUNCT__
@@ -71,6 +73,8 @@ static PetscErrorCode KSPSolve_B200(KSP ksp)
   o.norm_type     = (int)ksp->normtype;                         /* KSP_NORM_NONE..NATURAL == B200_KSP_NORM_* */
   o.guess_nonzero = ksp->guess_zero ? 0 : 1;
   o.gmres_restart = (int)kb->restart;
+  o.gmres_cgs_refine  = (int)kb->refine;                        /* KSP_GMRES_CGS_REFINE_NEVER, _IFNEEDED, _ALWAYS = 0, 1, 2 */
+  o.gmres_modified_gs = kb->mgs ? 1 : 0;
   o.fused         = kb->fused ? 1 : 0;
   o.check_every   = (int)kb->check_every;
   histmax = ksp->max_it + 2;
@@ -120,6 +124,15 @@ static PetscErrorCode KSPSetFromOptions_B200(KSP ksp)
   PetscFunctionBegin;
   ierr = PetscOptionsHead("KSP B200 options");CHKERRQ(ierr);
   ierr = PetscOptionsInt("-ksp_gmres_restart","Number of Krylov search directions","KSPGMRESSetRestart",kb->restart,&kb->restart,PETSC_NULL);CHKERRQ(ierr);
+  if (kb->kind == 1) {
+    PetscBool flg;
+    ierr = PetscOptionsEnum("-ksp_gmres_cgs_refinement_type","Type of iterative refinement for classical (unmodified) Gram-Schmidt","KSPGMRESSetCGSRefinementType",
+                            KSPGMRESCGSRefinementTypes,(PetscEnum)kb->refine,(PetscEnum*)&kb->refine,PETSC_NULL);CHKERRQ(ierr);
+    ierr = PetscOptionsBoolGroupBegin("-ksp_gmres_classicalgramschmidt","Classical (unmodified) Gram-Schmidt (fast)","KSPGMRESSetOrthogonalization",&flg);CHKERRQ(ierr);
+    if (flg) kb->mgs = PETSC_FALSE;
+    ierr = PetscOptionsBoolGroupEnd("-ksp_gmres_modifiedgramschmidt","Modified Gram-Schmidt (slow,more stable)","KSPGMRESSetOrthogonalization",&flg);CHKERRQ(ierr);
+    if (flg) kb->mgs = PETSC_TRUE;
+  }
   ierr = PetscOptionsInt("-ksp_b200_check_every","Iterations between host looks at the device-side convergence flag","",kb->check_every,&kb->check_every,PETSC_NULL);CHKERRQ(ierr);
   ierr = PetscOptionsBool("-ksp_b200_fused","Fused kernels (0: the reference's op-by-op sequence)","",kb->fused,&kb->fused,PETSC_NULL);CHKERRQ(ierr);
   ierr = PetscOptionsTail();CHKERRQ(ierr);
@@ -137,7 +150,8 @@ static PetscErrorCode KSPView_B200(KSP ksp,PetscViewer viewer)
   PetscFunctionBegin;
   ierr = PetscObjectTypeCompare((PetscObject)viewer,PETSCVIEWERASCII,&iascii);CHKERRQ(ierr);
   if (iascii) {
-    if (kb->kind) { ierr = PetscViewerASCIIPrintf(viewer,"  GMRES on the B200: restart=%D, classical Gram-Schmidt (one VecMDot + one VecMAXPY kernel pass per step)\n",kb->restart);CHKERRQ(ierr); }
+    if (kb->kind && kb->mgs) { ierr = PetscViewerASCIIPrintf(viewer,"  GMRES on the B200: restart=%D, modified Gram-Schmidt (one VecDot + one VecAXPY per basis vector)\n",kb->restart);CHKERRQ(ierr); }
+    else if (kb->kind) { ierr = PetscViewerASCIIPrintf(viewer,"  GMRES on the B200: restart=%D, classical Gram-Schmidt (one VecMDot + one VecMAXPY kernel pass per step), %s\n",kb->restart,KSPGMRESCGSRefinementTypes[kb->refine]);CHKERRQ(ierr); }
     else          { ierr = PetscViewerASCIIPrintf(viewer,"  CG on the B200: %s, host checks every %D iterations\n",kb->fused ? "fused kernels" : "op-by-op sequence",kb->check_every);CHKERRQ(ierr); }
   }
   PetscFunctionReturn(0);

@@ -35,6 +35,10 @@ CASES = {
                                   b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200", "-ksp_type", "cgb200"], history=True),
     "ksp_ex2_gmresb200": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "33", "-n", "41", "-pc_type", "jacobi", "-ksp_gmres_restart", "30"],
                               ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
+    "ksp_ex2_gmresb200_mgs": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "21", "-n", "23", "-pc_type", "jacobi", "-ksp_gmres_modifiedgramschmidt"],
+                                  ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
+    "ksp_ex2_gmresb200_refine": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "19", "-n", "27", "-pc_type", "jacobi", "-ksp_gmres_cgs_refinement_type", "refine_always"],
+                                     ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
     # src/ksp/ksp/examples/tutorials/makefile:410 — two systems, same nonzero structure, different values: the second
     # assembly reaches the device as a value-only refresh (no re-binning, no new exchange plan)
     "ksp_ex5_1": dict(prog="ksp_ex5", args=["-pc_type", "jacobi", "-ksp_monitor_short", "-ksp_gmres_cgs_refinement_type", "refine_always"],

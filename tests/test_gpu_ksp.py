@@ -34,6 +34,7 @@ def _solve_both(gpu, R, ip, j, a, n, bh, ksp, pc, rtol=1e-8, tol=1e-10, **kw):
     if kw.get("gmres_cgs_refine") == 2: opts["-ksp_gmres_cgs_refinement_type"] = "refine_always"
     if kw.get("gmres_cgs_refine") == 1: opts["-ksp_gmres_cgs_refinement_type"] = "refine_ifneeded"
     if "gmres_restart" in kw: opts["-ksp_gmres_restart"] = str(kw["gmres_restart"])
+    if kw.get("gmres_modified_gs"): opts["-ksp_gmres_modifiedgramschmidt"] = ""
     x0 = kw.pop("x0", None)
     rr = ref.ksp_solve(bh, ksp, pc, rtol=rtol, maxit=kw.get("max_it", 10000), x0=x0, options=opts)
     out = []
@@ -134,6 +135,16 @@ def test_gmres_jacobi(gpu, R, P, refine):
     n = 4000
     bh = R.RefMat(n, n, ip, j, a).mult(np.ones(n))
     _solve_both(gpu, R, ip, j, a, n, bh, "gmres", "jacobi", gmres_cgs_refine=refine)
+
+
+def test_gmres_modified_gram_schmidt(gpu, R, P):
+    """KSPGMRESModifiedGramSchmidtOrthogonalization (borthog.c:30-52): one VecDot + VecAXPY per basis vector."""
+    ip, j, a = P.powerlaw(4000, seed=4, xm=6.0, lmax=600)
+    n = 4000
+    bh = R.RefMat(n, n, ip, j, a).mult(np.ones(n))
+    _solve_both(gpu, R, ip, j, a, n, bh, "gmres", "jacobi", gmres_modified_gs=1)
+    ip, j, a = P.laplace2d_5pt(30, 30)
+    _solve_both(gpu, R, ip, j, a, 900, P.random_vector(900, 4), "gmres", "jacobi", rtol=1e-6, gmres_restart=12, gmres_modified_gs=1, tol=1e-8)
 
 
 def test_gmres_restarts_and_guess(gpu, R, P):
