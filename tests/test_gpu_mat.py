@@ -315,3 +315,33 @@ def test_mult_transpose_strips_and_refresh(gpu, R, P):
     B.update_values(a2)
     B.mult_transpose(x, z)
     assert np.array_equal(z.get_array(), R.RefMat(m, n, ip, j, a2, no_inode=True).multtranspose(xh))
+
+
+def test_against_the_inode_kernel(gpu, R, P):
+    """C5 (bs = 3): by default the reference multiplies this matrix with MatMult_SeqAIJ_Inode (inode.c:392-580), which
+    adds two products per step and so rounds differently from MatMult_SeqAIJ.  The device types switch inodes off like
+    the reference's own GPU type (aijcusp.cu:665) and are bit-identical to the plain kernel (tests above); against
+    the Inode kernel the results must still agree within the north-star tolerance 1e-12 * sum |a_ij x_j|."""
+    nx = 10
+    n = 3 * nx ** 3
+    ip, j, a = P.elasticity_bs3(nx)
+    ref = R.RefMat(n, n, ip, j, a, bs=3)                      # inode path (default options)
+    assert ref.inode_info()[0]
+    A = gpu.Mat.from_csr(n, n, ip, j, a)
+    xh, yh = P.random_vector(n, 2), P.random_vector(n, 3)
+    x, y, z = gpu.Vec(n, xh), gpu.Vec(n, yh), gpu.Vec(n)
+    A.mult(x, z)
+    scale = np.bincount(np.repeat(np.arange(n), np.diff(ip)), weights=np.abs(a * xh[j]), minlength=n)
+    assert np.all(np.abs(z.get_array() - ref.mult(xh)) <= 1e-12 * scale)
+    A.mult_add(x, y, z)
+    assert np.all(np.abs(z.get_array() - ref.multadd(xh, yh)) <= 1e-12 * (scale + np.abs(yh)))
+    # and the solver on top of it: same iteration count, history within 1e-10
+    b = ref.mult(np.ones(n))
+    rr = ref.ksp_solve(b, "cg", "jacobi", rtol=1e-8)
+    bv, xv = gpu.Vec(n, b), gpu.Vec(n)
+    r = gpu.ksp_solve(A, bv, xv, ksp_type="cg", pc_type="jacobi", rtol=1e-8)
+    assert abs(r["its"] - rr["its"]) <= 1
+    k = min(len(r["history"]), len(rr["history"]))
+    h, hr = np.asarray(r["history"][:k]), np.asarray(rr["history"][:k])
+    gate = hr > 1e-6 * hr[0]
+    assert np.max(np.abs(h[gate] - hr[gate]) / hr[gate]) <= 1e-10
