@@ -444,6 +444,8 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
       per = 1;
       while (per < (size_t)hstat.maxfat) per <<= 1;
       if (g > B200_NSM) g = B200_NSM;
+      const size_t room = (size_t)1 << 27;                  /* at most 1 GiB of scratch keys: fewer CTAs for gigantic rows */
+      if (per * (size_t)g > room) g = per >= room ? 1 : (int)(room / per);
       B200_CUDA(tmp.get(&scratch, per * (size_t)g));
     }
     asm_sort_cta_kernel<<<g, 512, 0, st>>>(hstat.nbig, big, nl, n, off, occ, d_rows, perm, rowlen, dstat, scratch, per); B200_LAUNCHED(1);
