@@ -158,6 +158,16 @@ int b200_mat_update_values_mpiaij(b200_mat A, const double *a_diag_host, const d
 int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
                             int on_device, int keep_plan, b200_mat *A);
 int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mats, int on_device);
+/* The local rows of a parallel matrix (MatSetValuesBatch on MPIAIJ; the reference's device version is
+ * MatSetValuesBatch_MPIAIJCUSP, src/mat/impls/aij/mpi/mpicusp/mpiaijAssemble.cu:200-460): rows rstart .. rstart+m_local
+ * of the global N x N matrix are assembled from the element list, ids of rows owned elsewhere are passed over as rows
+ * and kept as (global) column ids — what MatSetValues_MPIAIJ does with owned rows (mpiaij.c:496-570).  The result is a
+ * sequential m_local x N matrix with global column ids: the input of the diagonal / off-diagonal split
+ * (b200_mpiaij_split).  The caller first hands every rank the elements that touch its rows (the reference ships such
+ * entries through the stash at MatAssemblyBegin, mpiaij.c:630-650; petsc-dev_b200/parallel.py does it with one
+ * exchange of whole elements). */
+int b200_mat_setvaluesbatch_rows(int m_local, int rstart, int N, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                                 int on_device, int keep_plan, b200_mat *A);
 /* Copy the device CSR of a sequential matrix back to host arrays (i: m+1, j/a: nz; any may be NULL) —
  * MatCUSPCopyFromGPU, aijcusp.cu:187. */
 int b200_mat_get_csr(b200_mat A, int *i_host, int *j_host, double *a_host);

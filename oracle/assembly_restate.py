@@ -14,7 +14,10 @@ reference's golden output src/ksp/ksp/examples/tutorials/output/ex4_0.out.
 import numpy as np
 
 
-def setvaluesbatch(m, n, elem_rows, elem_mats, nl):
+def setvaluesbatch(m, n, elem_rows, elem_mats, nl, rstart=None):
+    """rstart=None: the sequential m x n matrix.  rstart given: the local rows rstart .. rstart+m of a parallel matrix
+    with n global columns — entries of rows owned elsewhere are left out (MatSetValues_MPIAIJ stashes them for their
+    owner, mpiaij.c:496-570; the owner gets them by assembling the same element), column ids stay global."""
     rows = np.asarray(elem_rows, dtype=np.int64).reshape(-1, nl)
     vals = np.asarray(elem_mats, dtype=np.float64).reshape(-1, nl, nl)
     ne = rows.shape[0]
@@ -22,6 +25,11 @@ def setvaluesbatch(m, n, elem_rows, elem_mats, nl):
     c = np.tile(rows, (1, nl)).reshape(-1)                       # column            = rows[e, b]
     v = vals.reshape(-1)
     keep = (r >= 0) & (c >= 0)
+    if rstart is not None:
+        if np.any(r[keep] >= n):
+            raise IndexError("row too large")
+        keep &= (r >= rstart) & (r < rstart + m)
+        r = r - rstart
     if np.any(r[keep] >= m) or np.any(c[keep] >= n):
         raise IndexError("row/column too large")
     r, c, v = r[keep], c[keep], v[keep]

@@ -182,21 +182,29 @@ static int dev_exclusive_scan(int n, const int *in, int *out, DevBufs &tmp, cuda
 }
 
 /* ---- steps 1, 2: occurrences of every row ------------------------------------------------------------------------- */
-__global__ void asm_count_kernel(long long nocc, const int *__restrict__ rows, int m, int *__restrict__ cnt, AsmStat *st)
+/* Row window [rstart, rstart + m): the sequential matrix has rstart = 0 and row_limit = m (a larger id is an error);
+ * the local rows of a parallel matrix have row_limit = global size, and ids of rows other ranks own are passed over
+ * here — they still serve as column ids in step 3 (MatSetValues_MPIAIJ keeps the owned rows and stashes the others,
+ * mpiaij.c:496-570). */
+__global__ void asm_count_kernel(long long nocc, const int *__restrict__ rows, int rstart, int m, int row_limit, int *__restrict__ cnt, AsmStat *st)
 {
   for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < nocc; o += (long long)gridDim.x * blockDim.x) {
-    const int r = rows[o];
-    if (r < 0) continue;                                   /* aij.c:311: negative rows are ignored */
-    if (r >= m) { atomicMax(&st->bad_row, r); continue; }
+    const int g = rows[o];
+    if (g < 0) continue;                                   /* aij.c:311: negative rows are ignored */
+    if (g >= row_limit) { atomicMax(&st->bad_row, g); continue; }
+    const int r = g - rstart;
+    if (r < 0 || r >= m) continue;                          /* another rank's row */
     atomicAdd(&cnt[r], 1);
   }
 }
 
 /* cnt counts down to zero while the slots fill from the back; the order inside a row is fixed later by the sort */
-__global__ void asm_fill_kernel(long long nocc, const int *__restrict__ rows, int m, const int *__restrict__ off, int *__restrict__ cnt, u32 *__restrict__ occ)
+__global__ void asm_fill_kernel(long long nocc, const int *__restrict__ rows, int rstart, int m, const int *__restrict__ off, int *__restrict__ cnt, u32 *__restrict__ occ)
 {
   for (long long o = (long long)blockIdx.x * blockDim.x + threadIdx.x; o < nocc; o += (long long)gridDim.x * blockDim.x) {
-    const int r = rows[o];
+    const int g = rows[o];
+    if (g < 0) continue;
+    const int r = g - rstart;
     if (r < 0 || r >= m) continue;
     const int pos = atomicSub(&cnt[r], 1) - 1;
     occ[off[r] + pos] = (u32)o;
@@ -386,8 +394,24 @@ static int grid_for(long long n, int threads)
   return (int)g;
 }
 
+static int setvaluesbatch_window(int m, int rstart, int row_limit, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                                 int on_device, int keep_plan, b200_mat *A);
+
 extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
                                        int on_device, int keep_plan, b200_mat *A)
+{
+  return setvaluesbatch_window(m, 0, m, n, ne, nl, elem_rows, elem_mats, on_device, keep_plan, A);
+}
+
+extern "C" int b200_mat_setvaluesbatch_rows(int m_local, int rstart, int N, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                                            int on_device, int keep_plan, b200_mat *A)
+{
+  if (rstart < 0 || (long long)rstart + m_local > N) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "rows %d..%d are not inside 0..%d", rstart, rstart + m_local, N);
+  return setvaluesbatch_window(m_local, rstart, N, N, ne, nl, elem_rows, elem_mats, on_device, keep_plan, A);
+}
+
+static int setvaluesbatch_window(int m, int rstart, int row_limit, int n, long long ne, int nl, const int *elem_rows, const double *elem_mats,
+                                 int on_device, int keep_plan, b200_mat *A)
 {
   B200_NEED_INIT();
   if (!A) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
@@ -426,13 +450,13 @@ extern "C" int b200_mat_setvaluesbatch(int m, int n, long long ne, int nl, const
   B200_CUDA(cudaMemcpyAsync(dstat, &hstat, sizeof(hstat), cudaMemcpyHostToDevice, st));
   B200_CUDA(cudaMemsetAsync(cnt, 0, sizeof(int) * ((size_t)m + 1), st));
   /* 1, 2: occurrence lists */
-  asm_count_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, m, cnt, dstat); B200_LAUNCHED(1);
+  asm_count_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, rstart, m, row_limit, cnt, dstat); B200_LAUNCHED(1);
   B200_CHK(dev_exclusive_scan(m, cnt, off, tmp, st));
-  asm_fill_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, m, off, cnt, occ); B200_LAUNCHED(1);
+  asm_fill_kernel<<<grid_for(nocc, 256), 256, 0, st>>>(nocc, d_rows, rstart, m, off, cnt, occ); B200_LAUNCHED(1);
   asm_classify_kernel<<<grid_for(m, 256), 256, 0, st>>>(m, nl, off, big, dstat); B200_LAUNCHED(1);
   B200_CUDA(cudaMemcpyAsync(&hstat, dstat, sizeof(hstat), cudaMemcpyDeviceToHost, st));
   B200_CUDA(cudaStreamSynchronize(st));
-  if (hstat.bad_row >= 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Row too large: row %d max %d", hstat.bad_row, m - 1);
+  if (hstat.bad_row >= 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Row too large: row %d max %d", hstat.bad_row, row_limit - 1);
   trace.mark("occurrence lists");
   /* 3: per-row sort */
   asm_sort_warp_kernel<<<grid_for(m, ASM_WARPS), ASM_WARPS * 32, 0, st>>>(m, nl, n, off, occ, d_rows, perm, rowlen, dstat); B200_LAUNCHED(1);

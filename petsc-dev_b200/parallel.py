@@ -235,3 +235,65 @@ def create_scatter(rank, size, ranges, inidx, inidy, ny, bs=1, dist=None, device
                                  int(frm["nfrom"]), _ip(fp), _ip(fs), _ip(fi), int(tl.size), _ip(tl), _ip(fl), C.byref(h)),
          "VecScatterCreate")
     return Scatter(h, rend - rstart, int(ny))
+
+
+# ---- MatSetValuesBatch on the parallel type (src/mat/impls/aij/mpi/mpicusp/mpiaijAssemble.cu:200-460) ----------------
+def batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist=None, device="cpu"):
+    """Hand every rank the elements that touch its rows.  The reference ships the (i, j, v) entries of rows a rank does
+    not own through the stash (MatAssemblyBegin_MPIAIJ, mpiaij.c:630-650; MPI_Alltoallv of rows/cols/values in
+    mpiaijAssemble.cu:326-352); whole elements are sent here instead, so the owner assembles them with the same
+    kernel and simply passes over the rows that are not its own.
+    Returns (rows, mats): this rank's own elements first, then what ranks 0, 1, ... sent, in their order."""
+    import torch
+    import torch.distributed as td
+    dist = dist or td
+    rows = np.ascontiguousarray(np.asarray(elem_rows, dtype=np.int32).reshape(-1, nl))
+    mats = np.ascontiguousarray(np.asarray(elem_mats, dtype=np.float64).reshape(-1, nl * nl))
+    if size == 1:
+        return rows.reshape(-1), mats.reshape(-1)
+    owner = np.searchsorted(np.asarray(ranges), rows, side="right") - 1          # -1 for negative (ignored) ids
+    owner[rows < 0] = -1
+    send = []                                                                     # element numbers per destination
+    for r in range(size):
+        send.append(np.nonzero(np.any(owner == r, axis=1))[0] if r != rank else np.zeros(0, np.int64))
+    counts = torch.tensor([s.size for s in send], dtype=torch.int64, device=device)
+    allc = [torch.zeros(size, dtype=torch.int64, device=device) for _ in range(size)]
+    dist.all_gather(allc, counts)
+    allc = torch.stack(allc).cpu().numpy()                                        # allc[s][d] = elements s sends to d
+    maxlen = max(int(allc.sum(axis=1).max()), 1)
+    order = np.concatenate(send) if size else np.zeros(0, np.int64)
+    myr = torch.zeros((maxlen, nl), dtype=torch.int32, device=device)
+    mym = torch.zeros((maxlen, nl * nl), dtype=torch.float64, device=device)
+    if order.size:
+        myr[:order.size] = torch.from_numpy(rows[order]).to(device)
+        mym[:order.size] = torch.from_numpy(mats[order]).to(device)
+    allr = [torch.zeros_like(myr) for _ in range(size)]
+    allm = [torch.zeros_like(mym) for _ in range(size)]
+    dist.all_gather(allr, myr)
+    dist.all_gather(allm, mym)
+    out_r, out_m = [rows], [mats]
+    for s in range(size):
+        c = int(allc[s][rank])
+        if s == rank or c == 0:
+            continue
+        off = int(allc[s][:rank].sum())
+        out_r.append(allr[s][off:off + c].cpu().numpy())
+        out_m.append(allm[s][off:off + c].cpu().numpy())
+    return np.concatenate(out_r).reshape(-1), np.concatenate(out_m).reshape(-1)
+
+
+def set_values_batch_mpiaij(rank, size, ranges, N, nl, elem_rows, elem_mats, bs=1, dist=None, device="cpu", return_host=False):
+    """MatSetValuesBatch + MatAssemblyBegin/End on a parallel matrix: exchange the interface elements, assemble this
+    rank's rows on the device (b200_mat_setvaluesbatch_rows: local rows x global columns), split into the diagonal
+    and off-diagonal blocks and build the ghost exchange exactly as for any other MPIAIJ matrix."""
+    rows, mats = batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist, device)
+    rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
+    h = C.c_void_p()
+    _chk(lib.b200_mat_setvaluesbatch_rows(rend - rstart, rstart, int(N), C.c_longlong(rows.size // nl), int(nl), _ip(rows), _dp(mats),
+                                          0, 0, C.byref(h)), "MatSetValuesBatch (local rows)")
+    L = Mat(h, rend - rstart, int(N))
+    ai, aj, aa = L.csr()
+    L.destroy()
+    host = setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=bs, dist=dist, device=device)
+    A = create_mpiaij(host)
+    return (A, (ai, aj, aa)) if return_host else A

@@ -191,6 +191,30 @@ def main():
             ok = ok and np.array_equal(x.get_array(), want[rs:re_])
         sc["bs%d" % bs] = bool(ok)
         del S
+    # ---- MatSetValuesBatch on the parallel type: every rank brings a chunk of the element list, interface elements
+    # travel to the owners of the rows they touch, the local rows are assembled on the device ----
+    N, nl, er, em = P.elements_hex3d(14)
+    ne = er.size // nl
+    e0, e1 = ne * rank // world, ne * (rank + 1) // world
+    ranges = par.split_ownership(N, world)
+    rs, re_ = int(ranges[rank]), int(ranges[rank + 1])
+    Ab, (bi, bj, ba) = par.set_values_batch_mpiaij(rank, world, ranges, N, nl, er[e0 * nl:e1 * nl], em[e0 * nl * nl:e1 * nl * nl],
+                                                   dist=dist, device="cuda", return_host=True)
+    from oracle import assembly_restate as AR
+    gi, gj, ga = AR.setvaluesbatch(N, N, er, em, nl)             # the whole matrix, every rank for itself
+    lo, hi = gi[rs], gi[re_]
+    batch_ok = bool(np.array_equal(bi, gi[rs:re_ + 1] - lo) and np.array_equal(bj, gj[lo:hi]) and
+                    np.all(np.abs(ba - ga[lo:hi]) <= 1e-13 * np.maximum(np.abs(ga[lo:hi]), 1.0)))
+    xg = P.random_vector(N, 5)
+    xb, yb = pb.Vec(re_ - rs, xg[rs:re_]), pb.Vec(re_ - rs)
+    Ab.mult(xb, yb)
+    want = np.array([np.dot(ga[gi[r]:gi[r + 1]], xg[gj[gi[r]:gi[r + 1]]]) for r in range(rs, re_)])
+    sc_rows = np.array([np.sum(np.abs(ga[gi[r]:gi[r + 1]] * xg[gj[gi[r]:gi[r + 1]]])) for r in range(rs, re_)])
+    batch_ok = batch_ok and bool(np.all(np.abs(yb.get_array() - want) <= 1e-12 * np.maximum(sc_rows, 1e-300)))
+    bk = torch.tensor([1.0 if batch_ok else 0.0], device="cuda")
+    dist.all_reduce(bk, op=dist.ReduceOp.MIN)
+    out["batch_assembly_ok"] = bool(bk.item() == 1.0)
+    del Ab
     oks = torch.tensor([1.0 if all(sc.values()) else 0.0], device="cuda")
     dist.all_reduce(oks, op=dist.ReduceOp.MIN)
     out["scatter"] = dict(sc, all_ranks=bool(oks.item() == 1.0))

@@ -82,3 +82,82 @@ def test_out_of_range_is_an_error():
     er = np.array([0, 1, 9], np.int32)
     with pytest.raises(IndexError):
         AR.setvaluesbatch(5, 5, er, np.ones(9), 3)
+
+
+# ---- parallel matrix: who gets which element (petsc-dev_b200/parallel.py::batch_exchange) ---------------------------
+def expected_after_exchange(ranges, parts, nl, rank):
+    """Own elements first, then — sender by sender, in the sender's order — the elements that touch this rank's rows."""
+    rows = [parts[rank][0].reshape(-1, nl)]
+    mats = [parts[rank][1].reshape(-1, nl * nl)]
+    for s, (er, em) in enumerate(parts):
+        if s == rank:
+            continue
+        er2 = er.reshape(-1, nl)
+        hit = np.any((er2 >= ranges[rank]) & (er2 < ranges[rank + 1]), axis=1)
+        rows.append(er2[hit]); mats.append(em.reshape(-1, nl * nl)[hit])
+    return np.concatenate(rows).reshape(-1), np.concatenate(mats).reshape(-1)
+
+
+def split_elements(er, em, nl, size):
+    """Contiguous chunks of the element list, one per rank (so interface elements touch rows of two ranks)."""
+    ne = er.size // nl
+    cut = [ne * r // size for r in range(size + 1)]
+    return [(er[cut[r] * nl:cut[r + 1] * nl], em[cut[r] * nl * nl:cut[r + 1] * nl * nl]) for r in range(size)]
+
+
+def _gloo_batch_worker(rank, size, port, q):
+    import sys
+    sys.path.insert(0, ROOT)
+    import torch.distributed as td
+    td.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=size)
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    N, nl, er, em = P.elements_hex3d(7)
+    ranges = par.split_ownership(N, size)
+    mine = split_elements(er, em, nl, size)[rank]
+    rows, mats = par.batch_exchange(rank, size, ranges, mine[0], mine[1], nl)
+    q.put((rank, rows, mats))
+    td.barrier()
+    td.destroy_process_group()
+
+
+def test_gloo_batch_exchange_world_size_2():
+    import torch.multiprocessing as mp
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 31000 + os.getpid() % 2000
+    procs = [ctx.Process(target=_gloo_batch_worker, args=(r, 2, port, q)) for r in range(2)]
+    [p.start() for p in procs]
+    got = {}
+    for _ in range(2):
+        r, rows, mats = q.get(timeout=120)
+        got[r] = (rows, mats)
+    [p.join(60) for p in procs]
+    assert all(p.exitcode == 0 for p in procs)
+    N, nl, er, em = P.elements_hex3d(7)
+    ranges = par.split_ownership(N, 2)
+    parts = split_elements(er, em, nl, 2)
+    for r in range(2):
+        wr, wm = expected_after_exchange(ranges, parts, nl, r)
+        assert np.array_equal(got[r][0], wr) and np.array_equal(got[r][1], wm)
+        assert wr.size > parts[r][0].size                    # something did cross the interface
+
+
+@needs_ref
+@pytest.mark.parametrize("size", [2, 3])
+def test_restated_local_rows_add_up_to_the_reference_matrix(size):
+    """Exact-arithmetic data (small integers): the per-rank local-row assemblies of the exchanged element lists,
+    stacked, are bit-identical to the reference's assembly of the whole element list — whatever the order in which
+    the off-process contributions arrive (which the reference leaves to MPI)."""
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    N, nl, er, em = P.elements_hex3d(6, scale_values=False)
+    em = np.round(em * 3.0)                                   # -1, 0, 4 -> integers: every sum exact
+    ranges = par.split_ownership(N, size)
+    parts = split_elements(er, em, nl, size)
+    ri, rj, ra = R.mat_setvaluesbatch(N, N, er, em, nl).csr()
+    for r in range(size):
+        rows, mats = expected_after_exchange(ranges, parts, nl, r)
+        rs, re_ = int(ranges[r]), int(ranges[r + 1])
+        i, j, a = AR.setvaluesbatch(re_ - rs, N, rows, mats, nl, rstart=rs)
+        assert np.array_equal(i, ri[rs:re_ + 1] - ri[rs])
+        assert np.array_equal(j, rj[ri[rs]:ri[re_]]) and np.array_equal(a, ra[ri[rs]:ri[re_]])

@@ -117,3 +117,38 @@ def test_size_independent_properties(gpu, P):
     i2, j2, a2 = gpu.Mat.set_values_batch(N, N, nl, er, em).csr()
     assert same((i1, j1, a1), (i2, j2, a2))
     assert np.all(np.diff(j1)[np.setdiff1d(np.arange(j1.size - 1), i1[1:-1] - 1)] > 0)      # columns ascend inside every row
+
+
+@pytest.mark.parametrize("size", [2, 3])
+def test_local_rows_of_a_parallel_matrix(gpu, P, R, size):
+    """b200_mat_setvaluesbatch_rows on the element lists every (virtual) rank holds after the exchange: bit-identical
+    to the restatement with the row window, and — for exact data — to the rows of the reference's global assembly."""
+    import ctypes as C
+    from oracle import assembly_restate as AR
+    from test_assembly import expected_after_exchange, split_elements
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    pb = gpu
+    for exact in (False, True):
+        N, nl, er, em = P.elements_hex3d(9, scale_values=not exact)
+        if exact:
+            em = np.round(em * 3.0)
+        ranges = par.split_ownership(N, size)
+        parts = split_elements(er, em, nl, size)
+        ri, rj, ra = R.mat_setvaluesbatch(N, N, er, em, nl).csr()
+        for r in range(size):
+            rows, mats = expected_after_exchange(ranges, parts, nl, r)
+            rows, mats = np.ascontiguousarray(rows, dtype=np.int32), np.ascontiguousarray(mats)
+            rs, re_ = int(ranges[r]), int(ranges[r + 1])
+            h = C.c_void_p()
+            rc = pb.lib.b200_mat_setvaluesbatch_rows(re_ - rs, rs, N, C.c_longlong(rows.size // nl), nl,
+                                                     rows.ctypes.data_as(C.c_void_p), mats.ctypes.data_as(C.c_void_p), 0, 0, C.byref(h))
+            assert rc == 0, pb.lib.b200_last_error()
+            L = pb.Mat(h, re_ - rs, N)
+            got = L.csr()
+            assert same(got, AR.setvaluesbatch(re_ - rs, N, rows, mats, nl, rstart=rs))
+            assert np.array_equal(got[0], ri[rs:re_ + 1] - ri[rs]) and np.array_equal(got[1], rj[ri[rs]:ri[re_]])
+            want = ra[ri[rs]:ri[re_]]
+            if exact:
+                assert np.array_equal(got[2], want)
+            else:
+                assert np.all(np.abs(got[2] - want) <= 1e-13 * np.maximum(np.abs(want), 1.0))

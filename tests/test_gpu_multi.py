@@ -40,6 +40,7 @@ def test_mpiaij_across_gpus(world, transport):
     out = _launch(world, transport)
     assert out["world"] == world
     assert out["scatter"]["all_ranks"] and all(out["scatter"].values()), out["scatter"]    # general VecScatter, both modes
+    assert out["batch_assembly_ok"]                       # MatSetValuesBatch on the parallel type, every rank
     for name, res in out["cases"].items():
         assert res["mult_ok"] and res["multadd_ok"], (name, res)          # bit-exact for the stencils, 1e-12 for plaw
         assert res["multtranspose_ok"], (name, res)                        # reverse exchange with ADD_VALUES
