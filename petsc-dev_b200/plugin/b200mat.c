@@ -515,6 +515,105 @@ static PetscErrorCode MatDestroy_MPIAIJB200(Mat A)                              
   PetscFunctionReturn(0);
 }
 
+/* MatSetValuesBatch_MPIAIJCUSP (src/mat/impls/aij/mpi/mpicusp/mpiaijAssemble.cu:200-460).  The reference ships the
+ * (i,j,v) entries of rows this rank does not own to their owners (three MPI_Alltoallv, :326-352) and sorts diagonal and
+ * off-diagonal COO lists; here every rank receives the whole ELEMENTS that touch its rows, the device assembles the
+ * local rows from own + received elements (b200_mat_setvaluesbatch_rows passes over rows owned elsewhere and keeps
+ * their ids as global columns), and the result enters the host matrix through MatMPIAIJSetPreallocationCSR, which
+ * splits it into the two blocks and assembles.  The exchange is setup-time and kept simple: one MPI_Allgatherv of
+ * the interface elements (petsc-dev_b200/parallel.py::batch_exchange is the same sequence, tested on 2 ranks). */
+#undef __FUNCT__
+#define __FUNCT__ "MatSetValuesBatch_MPIAIJB200"
+static PetscErrorCode MatSetValuesBatch_MPIAIJB200(Mat J,PetscInt Ne,PetscInt Nl,PetscInt *elemRows,const PetscScalar *elemMats)
+{
+  MPI_Comm       comm = ((PetscObject)J)->comm;
+  PetscMPIInt    size,rank;
+  PetscInt       rstart,rend,m,N,ne = Ne,*rows = elemRows,*ci,*cj,e,a,p,s;
+  PetscInt       *allrows = 0,*recvrows = 0,*sendrows = 0;
+  PetscScalar    *allmats = 0,*recvmats = 0,*sendmats = 0,*ca;
+  const PetscScalar *mats = elemMats;
+  long long      nz;
+  b200_mat       dm;
+  PetscErrorCode ierr;
+
+  PetscFunctionBegin;
+  ierr = MPI_Comm_size(comm,&size);CHKERRQ(ierr);
+  ierr = MPI_Comm_rank(comm,&rank);CHKERRQ(ierr);
+  ierr = PetscLayoutSetUp(J->rmap);CHKERRQ(ierr);
+  ierr = PetscLayoutSetUp(J->cmap);CHKERRQ(ierr);
+  rstart = J->rmap->rstart; rend = J->rmap->rend; m = rend - rstart; N = J->cmap->N;
+  if (size > 1) {
+    PetscMPIInt *cnt,*allc,*rc,*rd,*mc,*md;
+    PetscInt    *mark,nsend = 0,off,nrecv = 0,q;
+    /* which of my elements touch rows of rank s (s != rank): counts, then the elements grouped by destination */
+    ierr = PetscMalloc2(size,PetscMPIInt,&cnt,size*size,PetscMPIInt,&allc);CHKERRQ(ierr);
+    ierr = PetscMalloc((size_t)Ne*size*sizeof(PetscInt)+1,&mark);CHKERRQ(ierr);
+    ierr = PetscMemzero(mark,(size_t)Ne*size*sizeof(PetscInt));CHKERRQ(ierr);
+    ierr = PetscMemzero(cnt,size*sizeof(PetscMPIInt));CHKERRQ(ierr);
+    for (e=0; e<Ne; e++) {
+      for (a=0; a<Nl; a++) {
+        PetscInt row = elemRows[e*Nl+a],owner;
+        if (row < 0) continue;                                                    /* ignored, aij.c:311 */
+        if (row >= J->rmap->N) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_ARG_OUTOFRANGE,"Row too large: row %D max %D",row,J->rmap->N-1);
+        ierr = PetscLayoutFindOwner(J->rmap,row,&owner);CHKERRQ(ierr);
+        if (owner != rank && !mark[(size_t)e*size+owner]) { mark[(size_t)e*size+owner] = 1; cnt[owner]++; nsend++; }
+      }
+    }
+    ierr = MPI_Allgather(cnt,size,MPI_INT,allc,size,MPI_INT,comm);CHKERRQ(ierr);  /* allc[s*size+d]: elements s sends to d */
+    ierr = PetscMalloc2((size_t)nsend*Nl+1,PetscInt,&sendrows,(size_t)nsend*Nl*Nl+1,PetscScalar,&sendmats);CHKERRQ(ierr);
+    for (s=0,q=0; s<size; s++) {
+      if (s == rank) continue;
+      for (e=0; e<Ne; e++) {
+        if (!mark[(size_t)e*size+s]) continue;
+        ierr = PetscMemcpy(sendrows+(size_t)q*Nl,elemRows+(size_t)e*Nl,Nl*sizeof(PetscInt));CHKERRQ(ierr);
+        ierr = PetscMemcpy(sendmats+(size_t)q*Nl*Nl,elemMats+(size_t)e*Nl*Nl,Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
+        q++;
+      }
+    }
+    ierr = PetscMalloc4(size,PetscMPIInt,&rc,size,PetscMPIInt,&rd,size,PetscMPIInt,&mc,size,PetscMPIInt,&md);CHKERRQ(ierr);
+    for (s=0,off=0; s<size; s++) {
+      PetscInt tot = 0,d;
+      for (d=0; d<size; d++) tot += allc[s*size+d];
+      rc[s] = (PetscMPIInt)(tot*Nl); mc[s] = (PetscMPIInt)(tot*Nl*Nl);
+      rd[s] = (PetscMPIInt)(off*Nl); md[s] = (PetscMPIInt)(off*Nl*Nl);
+      off += tot;
+      if (s != rank) nrecv += allc[s*size+rank];
+    }
+    ierr = PetscMalloc2((size_t)off*Nl+1,PetscInt,&recvrows,(size_t)off*Nl*Nl+1,PetscScalar,&recvmats);CHKERRQ(ierr);
+    ierr = MPI_Allgatherv(sendrows,(PetscMPIInt)(nsend*Nl),MPIU_INT,recvrows,rc,rd,MPIU_INT,comm);CHKERRQ(ierr);
+    ierr = MPI_Allgatherv(sendmats,(PetscMPIInt)(nsend*Nl*Nl),MPIU_SCALAR,recvmats,mc,md,MPIU_SCALAR,comm);CHKERRQ(ierr);
+    /* own elements first, then what ranks 0,1,... sent me, in their order */
+    ne = Ne + nrecv;
+    ierr = PetscMalloc2((size_t)ne*Nl+1,PetscInt,&allrows,(size_t)ne*Nl*Nl+1,PetscScalar,&allmats);CHKERRQ(ierr);
+    ierr = PetscMemcpy(allrows,elemRows,(size_t)Ne*Nl*sizeof(PetscInt));CHKERRQ(ierr);
+    ierr = PetscMemcpy(allmats,elemMats,(size_t)Ne*Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
+    for (s=0,p=Ne; s<size; s++) {
+      PetscInt before = 0,d,c = allc[s*size+rank];
+      if (s == rank || !c) continue;
+      for (d=0; d<rank; d++) before += allc[s*size+d];
+      ierr = PetscMemcpy(allrows+(size_t)p*Nl,recvrows+rd[s]+(size_t)before*Nl,(size_t)c*Nl*sizeof(PetscInt));CHKERRQ(ierr);
+      ierr = PetscMemcpy(allmats+(size_t)p*Nl*Nl,recvmats+md[s]+(size_t)before*Nl*Nl,(size_t)c*Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
+      p += c;
+    }
+    rows = allrows; mats = allmats;
+    ierr = PetscFree4(rc,rd,mc,md);CHKERRQ(ierr);
+    ierr = PetscFree2(recvrows,recvmats);CHKERRQ(ierr);
+    ierr = PetscFree2(sendrows,sendmats);CHKERRQ(ierr);
+    ierr = PetscFree(mark);CHKERRQ(ierr);
+    ierr = PetscFree2(cnt,allc);CHKERRQ(ierr);
+  }
+  ierr = PetscInfo3(J,"Assembling rows %D..%D from %D element matrices on the device\n",rstart,rend,ne);CHKERRQ(ierr);
+  CHKB200(b200_mat_setvaluesbatch_rows(m,rstart,N,(long long)ne,Nl,rows,mats,0,0,&dm));
+  CHKB200(b200_mat_get_size(dm,0,0,&nz));
+  ierr = PetscMalloc3(m+1,PetscInt,&ci,(size_t)nz+1,PetscInt,&cj,(size_t)nz+1,PetscScalar,&ca);CHKERRQ(ierr);
+  CHKB200(b200_mat_get_csr(dm,ci,cj,ca));
+  CHKB200(b200_mat_destroy(dm));
+  if (size > 1) { ierr = PetscFree2(allrows,allmats);CHKERRQ(ierr); }
+  ierr = MatMPIAIJSetPreallocationCSR(J,ci,cj,ca);CHKERRQ(ierr);                  /* splits into the two blocks, assembles */
+  ierr = PetscFree3(ci,cj,ca);CHKERRQ(ierr);
+  PetscFunctionReturn(0);
+}
+
 /* the device operator behind a seqaijb200 / mpiaijb200 matrix (uploaded or refreshed first), for the KSP types */
 #undef __FUNCT__
 #define __FUNCT__ "MatB200GetHandle"
@@ -557,6 +656,7 @@ PetscErrorCode MatCreate_MPIAIJB200(Mat A)
   A->ops->multtransposeadd = MatMultTransposeAdd_MPIAIJB200;
   A->ops->getvecs = MatGetVecs_MPIAIJB200;
   A->ops->destroy = MatDestroy_MPIAIJB200;
+  A->ops->setvaluesbatch = MatSetValuesBatch_MPIAIJB200;                          /* mpiaijcusp.cu:217 */
   ierr = PetscObjectChangeTypeName((PetscObject)A,MATMPIAIJB200);CHKERRQ(ierr);
   PetscFunctionReturn(0);
 }

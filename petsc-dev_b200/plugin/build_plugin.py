@@ -29,6 +29,8 @@ EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
     "vec_tut_ex1": "src/vec/vec/examples/tutorials/ex1.c",
     "vec_ex43": "src/vec/vec/examples/tests/ex43.c",
     "vec_ex21": "src/vec/vec/examples/tests/ex21.c",
+    # this repository's own driver (public PETSc API only): MatSetValuesBatch on the parallel type
+    "b200_batch_mpiaij": os.path.join(ROOT, "tests", "c", "batch_mpiaij.c"),
 }
 
 

@@ -45,6 +45,9 @@ CASES = {
                       b200_args=B200, golden="src/ksp/ksp/examples/tutorials/output/ex5_1.out"),
     "ksp_ex5_mpiaij": dict(prog="ksp_ex5", args=["-pc_type", "jacobi", "-ksp_monitor_short", "-ksp_gmres_cgs_refinement_type", "refine_always", "-m", "7"],
                            ref_args=["-mat_type", "mpiaij", "-vec_type", "mpi"], b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"]),
+    # MatSetValuesBatch on the parallel type (tests/c/batch_mpiaij.c: ex4's mesh through MatCreate/MatSetType(MATMPIAIJ))
+    "batch_mpiaij": dict(prog="b200_batch_mpiaij", args=["-X", "6", "-Y", "5"], ref_args=["-mat_type", "mpiaij"],
+                         b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"]),
     # src/mat/examples/tests/makefile:753,774,795
     "mat_ex5_11_A": dict(prog="mat_ex5", args=["-rectA"], ref_args=["-mat_type", "seqaij"], b200_args=["-mat_type", "seqaijb200", "-vec_type", "seqb200"],
                          golden="src/mat/examples/tests/output/ex5_11_A.out"),

@@ -139,3 +139,15 @@ def test_same_pattern_reassembly_refreshes_values_only(case, uploads):
     mine = [l for l in out.splitlines() if "MatB200CopyToDevice_%s" % uploads in l]
     assert sum("full upload" in l for l in mine) == 1, mine
     assert sum("values refreshed" in l for l in mine) >= 1, mine
+
+
+def test_parallel_matsetvaluesbatch_takes_the_device_path():
+    """tests/c/batch_mpiaij.c with -mat_type mpiaijb200: the -info line of MatSetValuesBatch_MPIAIJB200 shows the plugin's
+    op ran (the output itself is compared with the reference arm by test_reference_example_output[batch_mpiaij]), and the
+    3 x 3 grid gives the rows of the reference's golden ex4_0.out."""
+    c = CASES["batch_mpiaij"]
+    out = run(c["prog"], ["-X", "3", "-Y", "3", "-dll_prepend", PLUGIN] + c["b200_args"] + ["-info"])
+    assert "MatSetValuesBatch_MPIAIJB200" in out and "on the device" in out
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_goldens.json")))["ksp_ex4_0"]["rows"]
+    want = [("row %d: %s" % (r, " ".join("(%d, %g) " % (cc, v) for cc, v in row))).strip() for r, row in enumerate(gold)]
+    assert matview_rows(out) == want, out
