@@ -168,6 +168,15 @@ int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mats, int on_d
  * exchange of whole elements). */
 int b200_mat_setvaluesbatch_rows(int m_local, int rstart, int N, long long ne, int nl, const int *elem_rows, const double *elem_mats,
                                  int on_device, int keep_plan, b200_mat *A);
+/* The exchange plan of that step (host integer work, no GPU needed).  b200_batch_send_plan: counts[d] = how many of my
+ * elements touch rows of rank d != rank; send_elems (NULL on a sizing call, else sum(counts) entries) = their element
+ * numbers grouped by destination ascending.  Every rank publishes one buffer with its groups in that order and the
+ * counts; b200_batch_recv_plan turns the gathered counts all_counts[s*size+d] into where this rank's group starts in
+ * rank s's buffer (src_off[s], in elements) and how long it is (src_cnt[s]).  The receiver assembles its own elements
+ * followed by the groups of s = 0, 1, ... */
+int b200_batch_send_plan(int size, int rank, const int *range /* size+1 */, long long ne, int nl, const int *elem_rows,
+                         long long *counts /* size */, long long *send_elems);
+int b200_batch_recv_plan(int size, int rank, const long long *all_counts /* size*size */, long long *src_off /* size */, long long *src_cnt /* size */);
 /* Copy the device CSR of a sequential matrix back to host arrays (i: m+1, j/a: nz; any may be NULL) —
  * MatCUSPCopyFromGPU, aijcusp.cu:187. */
 int b200_mat_get_csr(b200_mat A, int *i_host, int *j_host, double *a_host);

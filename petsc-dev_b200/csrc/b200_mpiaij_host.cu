@@ -190,3 +190,63 @@ extern "C" int b200_mpiaij_use_block_is(int nghost, const int *garray, int bs, i
   *use = 1;
   return 0;
 }
+
+/* ---- MatSetValuesBatch on the parallel type: who gets which element -------------------------------------------------
+ * The reference routes the (i, j, v) entries of rows a rank does not own to their owners at assembly time (stash:
+ * MatAssemblyBegin_MPIAIJ mpiaij.c:630-650; MatSetValuesBatch_MPIAIJCUSP sends rows/cols/values with MPI_Alltoallv,
+ * mpiaijAssemble.cu:326-352).  Here whole elements travel: an element goes to every OTHER rank that owns one of its
+ * rows; the receiver assembles own + received elements and passes over the rows that are not its own.
+ * Pure integer work, shared by the PETSc plugin (MPI) and petsc-dev_b200/parallel.py (torch.distributed). */
+
+/* counts[d] = how many of my elements go to rank d (0 for d == rank).  send_elems (may be NULL on a sizing call)
+ * receives the element numbers grouped by destination rank ascending, element order kept inside a group. */
+extern "C" int b200_batch_send_plan(int size, int rank, const int *range, long long ne, int nl, const int *elem_rows,
+                                    long long *counts, long long *send_elems)
+{
+  if (!range || !counts || (ne > 0 && !elem_rows)) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (size < 1 || rank < 0 || rank >= size || ne < 0 || nl < 1) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "bad size/rank/ne/nl %d/%d/%lld/%d", size, rank, ne, nl);
+  const int N = range[size];
+  std::vector<char> hit((size_t)size);
+  std::vector<long long> pos((size_t)size + 1, 0);
+  for (int pass = 0; pass < (send_elems ? 2 : 1); pass++) {
+    if (pass == 1) {                                           /* group starts from the counts of pass 0 */
+      long long acc = 0;
+      for (int d = 0; d < size; d++) { pos[d] = acc; acc += counts[d]; }
+    } else {
+      for (int d = 0; d < size; d++) counts[d] = 0;
+    }
+    for (long long e = 0; e < ne; e++) {
+      std::fill(hit.begin(), hit.end(), 0);
+      for (int a = 0; a < nl; a++) {
+        const int row = elem_rows[e * nl + a];
+        if (row < 0) continue;                                 /* ignored ids, aij.c:311 */
+        if (row >= N) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "Row too large: row %d max %d", row, N - 1);
+        const int owner = (int)(std::upper_bound(range, range + size + 1, row) - range) - 1;   /* PetscLayoutFindOwner */
+        if (owner != rank) hit[owner] = 1;
+      }
+      for (int d = 0; d < size; d++) {
+        if (!hit[d]) continue;
+        if (pass == 0) counts[d]++;
+        else send_elems[pos[d]++] = e;
+      }
+    }
+  }
+  return 0;
+}
+
+/* all_counts[s*size + d] = elements rank s sends to rank d (the gathered counts of every rank).  Every rank publishes
+ * ONE buffer holding its groups in destination order; for the receiving rank: src_off[s] = first element of its group
+ * inside rank s's buffer, src_cnt[s] = its length (0 for s == rank).  The receiver appends the groups of s = 0, 1, ...
+ * after its own elements. */
+extern "C" int b200_batch_recv_plan(int size, int rank, const long long *all_counts, long long *src_off, long long *src_cnt)
+{
+  if (!all_counts || !src_off || !src_cnt) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (size < 1 || rank < 0 || rank >= size) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "bad size/rank %d/%d", size, rank);
+  for (int s = 0; s < size; s++) {
+    long long before = 0;
+    for (int d = 0; d < rank; d++) before += all_counts[(size_t)s * size + d];
+    src_off[s] = before;
+    src_cnt[s] = s == rank ? 0 : all_counts[(size_t)s * size + rank];
+  }
+  return 0;
+}

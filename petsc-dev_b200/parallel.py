@@ -251,19 +251,23 @@ def batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist=None, devi
     mats = np.ascontiguousarray(np.asarray(elem_mats, dtype=np.float64).reshape(-1, nl * nl))
     if size == 1:
         return rows.reshape(-1), mats.reshape(-1)
-    owner = np.searchsorted(np.asarray(ranges), rows, side="right") - 1          # -1 for negative (ignored) ids
-    owner[rows < 0] = -1
-    send = []                                                                     # element numbers per destination
-    for r in range(size):
-        send.append(np.nonzero(np.any(owner == r, axis=1))[0] if r != rank else np.zeros(0, np.int64))
-    counts = torch.tensor([s.size for s in send], dtype=torch.int64, device=device)
+    rg = _i32(ranges)
+    ne = rows.shape[0]
+    cnt = np.zeros(size, np.int64)
+    llp = C.POINTER(C.c_longlong)
+    _chk(lib.b200_batch_send_plan(int(size), int(rank), _ip(rg), C.c_longlong(ne), int(nl), _ip(rows), cnt.ctypes.data_as(llp), None),
+         "MatSetValuesBatch (send plan)")
+    order = np.zeros(max(int(cnt.sum()), 1), np.int64)
+    _chk(lib.b200_batch_send_plan(int(size), int(rank), _ip(rg), C.c_longlong(ne), int(nl), _ip(rows), cnt.ctypes.data_as(llp),
+                                  order.ctypes.data_as(llp)), "MatSetValuesBatch (send plan)")
+    order = order[:int(cnt.sum())]
+    counts = torch.tensor(cnt, dtype=torch.int64, device=device)
     allc = [torch.zeros(size, dtype=torch.int64, device=device) for _ in range(size)]
     dist.all_gather(allc, counts)
-    allc = torch.stack(allc).cpu().numpy()                                        # allc[s][d] = elements s sends to d
+    allc = np.ascontiguousarray(torch.stack(allc).cpu().numpy())                  # allc[s][d] = elements s sends to d
     maxlen = max(int(allc.sum(axis=1).max()), 1)
-    order = np.concatenate(send) if size else np.zeros(0, np.int64)
-    myr = torch.zeros((maxlen, nl), dtype=torch.int32, device=device)
-    mym = torch.zeros((maxlen, nl * nl), dtype=torch.float64, device=device)
+    myr = torch.zeros((maxlen, nl), dtype=torch.int32, device=device)           # one padded buffer per rank, groups in
+    mym = torch.zeros((maxlen, nl * nl), dtype=torch.float64, device=device)    # destination order
     if order.size:
         myr[:order.size] = torch.from_numpy(rows[order]).to(device)
         mym[:order.size] = torch.from_numpy(mats[order]).to(device)
@@ -271,14 +275,14 @@ def batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist=None, devi
     allm = [torch.zeros_like(mym) for _ in range(size)]
     dist.all_gather(allr, myr)
     dist.all_gather(allm, mym)
+    off, num = np.zeros(size, np.int64), np.zeros(size, np.int64)
+    _chk(lib.b200_batch_recv_plan(int(size), int(rank), allc.ctypes.data_as(llp), off.ctypes.data_as(llp), num.ctypes.data_as(llp)),
+         "MatSetValuesBatch (receive plan)")
     out_r, out_m = [rows], [mats]
     for s in range(size):
-        c = int(allc[s][rank])
-        if s == rank or c == 0:
-            continue
-        off = int(allc[s][:rank].sum())
-        out_r.append(allr[s][off:off + c].cpu().numpy())
-        out_m.append(allm[s][off:off + c].cpu().numpy())
+        if num[s]:
+            out_r.append(allr[s][int(off[s]):int(off[s] + num[s])].cpu().numpy())
+            out_m.append(allm[s][int(off[s]):int(off[s] + num[s])].cpu().numpy())
     return np.concatenate(out_r).reshape(-1), np.concatenate(out_m).reshape(-1)
 
 

@@ -521,14 +521,17 @@ static PetscErrorCode MatDestroy_MPIAIJB200(Mat A)                              
  * local rows from own + received elements (b200_mat_setvaluesbatch_rows passes over rows owned elsewhere and keeps
  * their ids as global columns), and the result enters the host matrix through MatMPIAIJSetPreallocationCSR, which
  * splits it into the two blocks and assembles.  The exchange is setup-time and kept simple: one MPI_Allgatherv of
- * the interface elements (petsc-dev_b200/parallel.py::batch_exchange is the same sequence, tested on 2 ranks). */
+ * the interface elements; who sends what and where a rank's share starts in a sender's buffer is decided by the
+ * library (b200_batch_send_plan / b200_batch_recv_plan — the same two functions petsc-dev_b200/parallel.py uses on
+ * real ranks and tests/test_assembly.py drives with virtual ranks), so only the two MPI calls below are specific to
+ * this file. */
 #undef __FUNCT__
 #define __FUNCT__ "MatSetValuesBatch_MPIAIJB200"
 static PetscErrorCode MatSetValuesBatch_MPIAIJB200(Mat J,PetscInt Ne,PetscInt Nl,PetscInt *elemRows,const PetscScalar *elemMats)
 {
   MPI_Comm       comm = ((PetscObject)J)->comm;
   PetscMPIInt    size,rank;
-  PetscInt       rstart,rend,m,N,ne = Ne,*rows = elemRows,*ci,*cj,e,a,p,s;
+  PetscInt       rstart,rend,m,N,ne = Ne,*rows = elemRows,*ci,*cj,p,s;
   PetscInt       *allrows = 0,*recvrows = 0,*sendrows = 0;
   PetscScalar    *allmats = 0,*recvmats = 0,*sendmats = 0,*ca;
   const PetscScalar *mats = elemMats;
@@ -543,64 +546,54 @@ static PetscErrorCode MatSetValuesBatch_MPIAIJB200(Mat J,PetscInt Ne,PetscInt Nl
   ierr = PetscLayoutSetUp(J->cmap);CHKERRQ(ierr);
   rstart = J->rmap->rstart; rend = J->rmap->rend; m = rend - rstart; N = J->cmap->N;
   if (size > 1) {
-    PetscMPIInt *cnt,*allc,*rc,*rd,*mc,*md;
-    PetscInt    *mark,nsend = 0,off,nrecv = 0,q;
-    /* which of my elements touch rows of rank s (s != rank): counts, then the elements grouped by destination */
-    ierr = PetscMalloc2(size,PetscMPIInt,&cnt,size*size,PetscMPIInt,&allc);CHKERRQ(ierr);
-    ierr = PetscMalloc((size_t)Ne*size*sizeof(PetscInt)+1,&mark);CHKERRQ(ierr);
-    ierr = PetscMemzero(mark,(size_t)Ne*size*sizeof(PetscInt));CHKERRQ(ierr);
-    ierr = PetscMemzero(cnt,size*sizeof(PetscMPIInt));CHKERRQ(ierr);
-    for (e=0; e<Ne; e++) {
-      for (a=0; a<Nl; a++) {
-        PetscInt row = elemRows[e*Nl+a],owner;
-        if (row < 0) continue;                                                    /* ignored, aij.c:311 */
-        if (row >= J->rmap->N) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_ARG_OUTOFRANGE,"Row too large: row %D max %D",row,J->rmap->N-1);
-        ierr = PetscLayoutFindOwner(J->rmap,row,&owner);CHKERRQ(ierr);
-        if (owner != rank && !mark[(size_t)e*size+owner]) { mark[(size_t)e*size+owner] = 1; cnt[owner]++; nsend++; }
-      }
-    }
-    ierr = MPI_Allgather(cnt,size,MPI_INT,allc,size,MPI_INT,comm);CHKERRQ(ierr);  /* allc[s*size+d]: elements s sends to d */
+    PetscMPIInt *rc,*rd,*mc,*md;
+    long long   *cnt,*allc,*order,*soff,*scnt,nsend = 0,total = 0,nrecv = 0,q;
+    int         *irange;
+    /* which of my elements touch rows of rank d != rank, grouped by destination (b200_batch_send_plan) */
+    ierr = PetscMalloc5(size,long long,&cnt,size*size,long long,&allc,size,long long,&soff,size,long long,&scnt,size+1,int,&irange);CHKERRQ(ierr);
+    for (s=0; s<=size; s++) irange[s] = (int)J->rmap->range[s];
+    CHKB200(b200_batch_send_plan(size,rank,irange,(long long)Ne,(int)Nl,elemRows,cnt,0));
+    for (s=0; s<size; s++) nsend += cnt[s];
+    ierr = PetscMalloc((nsend+1)*sizeof(long long),&order);CHKERRQ(ierr);
+    CHKB200(b200_batch_send_plan(size,rank,irange,(long long)Ne,(int)Nl,elemRows,cnt,order));
+    ierr = MPI_Allgather(cnt,size,MPI_LONG_LONG_INT,allc,size,MPI_LONG_LONG_INT,comm);CHKERRQ(ierr);   /* allc[s*size+d] */
     ierr = PetscMalloc2((size_t)nsend*Nl+1,PetscInt,&sendrows,(size_t)nsend*Nl*Nl+1,PetscScalar,&sendmats);CHKERRQ(ierr);
-    for (s=0,q=0; s<size; s++) {
-      if (s == rank) continue;
-      for (e=0; e<Ne; e++) {
-        if (!mark[(size_t)e*size+s]) continue;
-        ierr = PetscMemcpy(sendrows+(size_t)q*Nl,elemRows+(size_t)e*Nl,Nl*sizeof(PetscInt));CHKERRQ(ierr);
-        ierr = PetscMemcpy(sendmats+(size_t)q*Nl*Nl,elemMats+(size_t)e*Nl*Nl,Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
-        q++;
-      }
+    for (q=0; q<nsend; q++) {
+      ierr = PetscMemcpy(sendrows+(size_t)q*Nl,elemRows+(size_t)order[q]*Nl,Nl*sizeof(PetscInt));CHKERRQ(ierr);
+      ierr = PetscMemcpy(sendmats+(size_t)q*Nl*Nl,elemMats+(size_t)order[q]*Nl*Nl,Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
     }
+    /* every rank publishes its one buffer (groups in destination order); where mine start: b200_batch_recv_plan */
     ierr = PetscMalloc4(size,PetscMPIInt,&rc,size,PetscMPIInt,&rd,size,PetscMPIInt,&mc,size,PetscMPIInt,&md);CHKERRQ(ierr);
-    for (s=0,off=0; s<size; s++) {
-      PetscInt tot = 0,d;
-      for (d=0; d<size; d++) tot += allc[s*size+d];
+    for (s=0; s<size; s++) {
+      long long tot = 0;
+      PetscInt  d;
+      for (d=0; d<size; d++) tot += allc[(size_t)s*size+d];
       rc[s] = (PetscMPIInt)(tot*Nl); mc[s] = (PetscMPIInt)(tot*Nl*Nl);
-      rd[s] = (PetscMPIInt)(off*Nl); md[s] = (PetscMPIInt)(off*Nl*Nl);
-      off += tot;
-      if (s != rank) nrecv += allc[s*size+rank];
+      rd[s] = (PetscMPIInt)(total*Nl); md[s] = (PetscMPIInt)(total*Nl*Nl);
+      total += tot;
     }
-    ierr = PetscMalloc2((size_t)off*Nl+1,PetscInt,&recvrows,(size_t)off*Nl*Nl+1,PetscScalar,&recvmats);CHKERRQ(ierr);
+    CHKB200(b200_batch_recv_plan(size,rank,allc,soff,scnt));
+    for (s=0; s<size; s++) nrecv += scnt[s];
+    ierr = PetscMalloc2((size_t)total*Nl+1,PetscInt,&recvrows,(size_t)total*Nl*Nl+1,PetscScalar,&recvmats);CHKERRQ(ierr);
     ierr = MPI_Allgatherv(sendrows,(PetscMPIInt)(nsend*Nl),MPIU_INT,recvrows,rc,rd,MPIU_INT,comm);CHKERRQ(ierr);
     ierr = MPI_Allgatherv(sendmats,(PetscMPIInt)(nsend*Nl*Nl),MPIU_SCALAR,recvmats,mc,md,MPIU_SCALAR,comm);CHKERRQ(ierr);
     /* own elements first, then what ranks 0,1,... sent me, in their order */
-    ne = Ne + nrecv;
+    ne = Ne + (PetscInt)nrecv;
     ierr = PetscMalloc2((size_t)ne*Nl+1,PetscInt,&allrows,(size_t)ne*Nl*Nl+1,PetscScalar,&allmats);CHKERRQ(ierr);
     ierr = PetscMemcpy(allrows,elemRows,(size_t)Ne*Nl*sizeof(PetscInt));CHKERRQ(ierr);
     ierr = PetscMemcpy(allmats,elemMats,(size_t)Ne*Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
     for (s=0,p=Ne; s<size; s++) {
-      PetscInt before = 0,d,c = allc[s*size+rank];
-      if (s == rank || !c) continue;
-      for (d=0; d<rank; d++) before += allc[s*size+d];
-      ierr = PetscMemcpy(allrows+(size_t)p*Nl,recvrows+rd[s]+(size_t)before*Nl,(size_t)c*Nl*sizeof(PetscInt));CHKERRQ(ierr);
-      ierr = PetscMemcpy(allmats+(size_t)p*Nl*Nl,recvmats+md[s]+(size_t)before*Nl*Nl,(size_t)c*Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
-      p += c;
+      if (!scnt[s]) continue;
+      ierr = PetscMemcpy(allrows+(size_t)p*Nl,recvrows+rd[s]+(size_t)soff[s]*Nl,(size_t)scnt[s]*Nl*sizeof(PetscInt));CHKERRQ(ierr);
+      ierr = PetscMemcpy(allmats+(size_t)p*Nl*Nl,recvmats+md[s]+(size_t)soff[s]*Nl*Nl,(size_t)scnt[s]*Nl*Nl*sizeof(PetscScalar));CHKERRQ(ierr);
+      p += (PetscInt)scnt[s];
     }
     rows = allrows; mats = allmats;
     ierr = PetscFree4(rc,rd,mc,md);CHKERRQ(ierr);
     ierr = PetscFree2(recvrows,recvmats);CHKERRQ(ierr);
     ierr = PetscFree2(sendrows,sendmats);CHKERRQ(ierr);
-    ierr = PetscFree(mark);CHKERRQ(ierr);
-    ierr = PetscFree2(cnt,allc);CHKERRQ(ierr);
+    ierr = PetscFree(order);CHKERRQ(ierr);
+    ierr = PetscFree5(cnt,allc,soff,scnt,irange);CHKERRQ(ierr);
   }
   ierr = PetscInfo3(J,"Assembling rows %D..%D from %D element matrices on the device\n",rstart,rend,ne);CHKERRQ(ierr);
   CHKB200(b200_mat_setvaluesbatch_rows(m,rstart,N,(long long)ne,Nl,rows,mats,0,0,&dm));

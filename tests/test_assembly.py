@@ -161,3 +161,44 @@ def test_restated_local_rows_add_up_to_the_reference_matrix(size):
         i, j, a = AR.setvaluesbatch(re_ - rs, N, rows, mats, nl, rstart=rs)
         assert np.array_equal(i, ri[rs:re_ + 1] - ri[rs])
         assert np.array_equal(j, rj[ri[rs]:ri[re_]]) and np.array_equal(a, ra[ri[rs]:ri[re_]])
+
+
+@pytest.mark.parametrize("size", [1, 2, 3, 5])
+def test_exchange_plan_helpers_with_virtual_ranks(size):
+    """b200_batch_send_plan / b200_batch_recv_plan (the integer logic shared by the PETSc plugin's MPI path and
+    parallel.py) driven for every virtual rank in one process: publish one buffer per rank, pick the shares."""
+    import ctypes as C
+    pb = importlib.import_module("petsc-dev_b200")
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    llp = C.POINTER(C.c_longlong)
+    ip = C.POINTER(C.c_int)
+    N, nl, er, em = P.elements_tri2d(13, 9)
+    er = er.copy(); er[5] = -1                                  # an ignored id changes nothing about the routing of the rest
+    ranges = np.ascontiguousarray(par.split_ownership(N, size), dtype=np.int32)
+    parts = split_elements(er, em, nl, size)
+    bufs, counts = [], np.zeros((size, size), np.int64)
+    for r in range(size):
+        rows = np.ascontiguousarray(parts[r][0], dtype=np.int32)
+        ne = rows.size // nl
+        cnt = np.zeros(size, np.int64)
+        assert pb.lib.b200_batch_send_plan(size, r, ranges.ctypes.data_as(ip), C.c_longlong(ne), nl, rows.ctypes.data_as(ip),
+                                           cnt.ctypes.data_as(llp), None) == 0
+        order = np.zeros(max(int(cnt.sum()), 1), np.int64)
+        assert pb.lib.b200_batch_send_plan(size, r, ranges.ctypes.data_as(ip), C.c_longlong(ne), nl, rows.ctypes.data_as(ip),
+                                           cnt.ctypes.data_as(llp), order.ctypes.data_as(llp)) == 0
+        order = order[:int(cnt.sum())]
+        assert cnt[r] == 0
+        counts[r] = cnt
+        bufs.append((rows.reshape(-1, nl)[order], parts[r][1].reshape(-1, nl * nl)[order]))
+    for r in range(size):
+        off, num = np.zeros(size, np.int64), np.zeros(size, np.int64)
+        assert pb.lib.b200_batch_recv_plan(size, r, np.ascontiguousarray(counts).ctypes.data_as(llp), off.ctypes.data_as(llp),
+                                           num.ctypes.data_as(llp)) == 0
+        rows = [parts[r][0].reshape(-1, nl)] + [bufs[s][0][off[s]:off[s] + num[s]] for s in range(size) if num[s]]
+        mats = [parts[r][1].reshape(-1, nl * nl)] + [bufs[s][1][off[s]:off[s] + num[s]] for s in range(size) if num[s]]
+        wr, wm = expected_after_exchange(ranges, parts, nl, r)
+        assert np.array_equal(np.concatenate(rows).reshape(-1), wr) and np.array_equal(np.concatenate(mats).reshape(-1), wm)
+    bad = np.array([0, 1, N], np.int32)                         # a row beyond the matrix is an error, not a routing decision
+    cnt = np.zeros(size, np.int64)
+    assert pb.lib.b200_batch_send_plan(size, 0, ranges.ctypes.data_as(ip), C.c_longlong(1), 3, bad.ctypes.data_as(ip),
+                                       cnt.ctypes.data_as(llp), None) == 63
