@@ -83,3 +83,64 @@ def read_system(path):
         except PetscBinaryError:
             b = None
     return M, N, ai, aj, aa, b
+
+
+# ---- striped reads: every rank fetches its own row slab (MatLoad_MPIAIJ, src/mat/impls/aij/mpi/mpiaij.c:3416-3600, has
+# rank 0 read the file and send the slabs out; with one process per GPU and a shared file every rank seeks instead) ----
+def read_mat_header(path):
+    """-> (M, N, nz, offset of the row-length block)."""
+    with open(path, "rb") as f:
+        hdr = np.fromfile(f, dtype=">i4", count=4)
+    if hdr.size != 4 or hdr[0] != MAT_FILE_CLASSID:
+        raise PetscBinaryError("not a PETSc matrix file (classid %s)" % (hdr[0] if hdr.size else "missing"))
+    if hdr[3] < 0:
+        raise PetscBinaryError("dense-format matrix files (nz = -1) are not supported")
+    return int(hdr[1]), int(hdr[2]), int(hdr[3]), 16
+
+
+def read_mat_rows(path, r0, r1):
+    """Rows [r0, r1) only -> (M, N, ai[r1-r0+1] starting at 0, aj (global column ids), aa).  Reads the row lengths up to r1
+    (to locate the slab) and then exactly the slab's column ids and values."""
+    M, N, nz, off = read_mat_header(path)
+    if not (0 <= r0 <= r1 <= M):
+        raise PetscBinaryError("rows %d..%d are not inside 0..%d" % (r0, r1, M))
+    with open(path, "rb") as f:
+        f.seek(off)
+        lens = np.fromfile(f, dtype=">i4", count=r1).astype(np.int64)
+        if lens.size != r1:
+            raise PetscBinaryError("file ends inside the row lengths")
+        k0, k1 = int(lens[:r0].sum()), int(lens.sum())
+        if k1 > nz:
+            raise PetscBinaryError("row lengths exceed nz (Inconsistant matrix data in file, aij.c:4139)")
+        f.seek(off + 4 * M + 4 * k0)
+        aj = np.fromfile(f, dtype=">i4", count=k1 - k0)
+        f.seek(off + 4 * M + 4 * nz + 8 * k0)
+        aa = np.fromfile(f, dtype=">f8", count=k1 - k0)
+    if aj.size != k1 - k0 or aa.size != k1 - k0:
+        raise PetscBinaryError("file ends before the slab's %d entries were read" % (k1 - k0))
+    ai = np.zeros(r1 - r0 + 1, np.int32)
+    np.cumsum(lens[r0:r1], out=ai[1:])
+    return M, N, ai, aj.astype(np.int32), aa.astype(np.float64)
+
+
+def mat_file_size(path):
+    """Bytes the matrix occupies at the start of the file (a right-hand side, if any, follows)."""
+    M, N, nz, off = read_mat_header(path)
+    return off + 4 * M + 12 * nz
+
+
+def read_vec_rows(path, r0, r1, offset=0):
+    """Entries [r0, r1) of the vector that starts `offset` bytes into the file; None when no vector starts there."""
+    with open(path, "rb") as f:
+        f.seek(offset)
+        hdr = np.fromfile(f, dtype=">i4", count=2)
+        if hdr.size != 2 or hdr[0] != VEC_FILE_CLASSID:
+            return None
+        n = int(hdr[1])
+        if not (0 <= r0 <= r1 <= n):
+            raise PetscBinaryError("entries %d..%d are not inside 0..%d" % (r0, r1, n))
+        f.seek(offset + 8 + 8 * r0)
+        x = np.fromfile(f, dtype=">f8", count=r1 - r0)
+    if x.size != r1 - r0:
+        raise PetscBinaryError("file ends before %d entries were read" % (r1 - r0))
+    return x.astype(np.float64)

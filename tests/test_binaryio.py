@@ -68,3 +68,36 @@ def test_system_file_and_errors(bio, P, tmp_path):
         fh.truncate(200)
     with pytest.raises(bio.PetscBinaryError):
         bio.read_mat(f)
+
+
+def test_striped_reads_match_the_whole_file(bio, tmp_path, R, P):
+    """Every rank reads its own row slab with seeks: slabs of a file the REFERENCE wrote (matrix followed by a vector)
+    stack up to what the whole-file reader and the reference's MatLoad return."""
+    n = 1000
+    ip, j, a = P.powerlaw(n, seed=4, xm=3.0, lmax=200)
+    ref = R.RefMat(n, n, ip, j, a, no_inode=True)
+    path = str(tmp_path / "sys.bin")
+    R.mat_write_binary(ref, path)
+    bh = P.random_vector(n, 9)
+    vpath = str(tmp_path / "v.bin")
+    R.vec_write_binary(bh, vpath)
+    with open(path, "ab") as f:                              # ex10-style file: the vector follows the matrix
+        f.write(open(vpath, "rb").read())
+    M, N, ai, aj, aa, b = bio.read_system(path)
+    assert bio.mat_file_size(path) == 16 + 4 * M + 12 * len(aa)
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    for size in (1, 3, 7):
+        ranges = par.split_ownership(M, size)
+        rows, cols, vals, rhs = [0], [], [], []
+        for r in range(size):
+            r0, r1 = int(ranges[r]), int(ranges[r + 1])
+            m2, n2, si, sj, sa = bio.read_mat_rows(path, r0, r1)
+            assert (m2, n2) == (M, N) and si[0] == 0 and si.size == r1 - r0 + 1
+            rows += list(si[1:] + rows[-1]); cols.append(sj); vals.append(sa)
+            rhs.append(bio.read_vec_rows(path, r0, r1, offset=bio.mat_file_size(path)))
+        assert np.array_equal(np.array(rows, np.int32), ai)
+        assert np.array_equal(np.concatenate(cols), aj) and np.array_equal(np.concatenate(vals), aa)
+        assert np.array_equal(np.concatenate(rhs), b) and np.array_equal(b, bh)
+    assert bio.read_vec_rows(vpath, 0, 10, offset=4) is None          # no vector header there
+    with pytest.raises(bio.PetscBinaryError):
+        bio.read_mat_rows(path, 5, M + 1)
