@@ -6,8 +6,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pb = importlib.import_module("petsc-dev_b200"); P = importlib.import_module("petsc-dev_b200.problems")
 pb.init(0)
 n = 256 ** 3
-x, y = pb.Vec(n, P.random_vector(n, 1)), pb.Vec(n, P.random_vector(n, 2))
-vs = [pb.Vec(n, P.random_vector(n, 10 + k)) for k in range(32)]
+base = P.random_vector(n, 1)                    # one host vector for every buffer: bandwidth does not depend on the values
+x, y = pb.Vec(n, base), pb.Vec(n, base)
+vs = [pb.Vec(n, base) for k in range(32)]
 al = np.linspace(1e-4, 1e-3, 32)
 for nv in range(1, 33):
     res = []
