@@ -163,8 +163,9 @@ def test_restated_local_rows_add_up_to_the_reference_matrix(size):
         assert np.array_equal(j, rj[ri[rs]:ri[re_]]) and np.array_equal(a, ra[ri[rs]:ri[re_]])
 
 
+@pytest.mark.parametrize("mesh", ["tri", "hostile"])
 @pytest.mark.parametrize("size", [1, 2, 3, 5])
-def test_exchange_plan_helpers_with_virtual_ranks(size):
+def test_exchange_plan_helpers_with_virtual_ranks(size, mesh):
     """b200_batch_send_plan / b200_batch_recv_plan (the integer logic shared by the PETSc plugin's MPI path and
     parallel.py) driven for every virtual rank in one process: publish one buffer per rank, pick the shares."""
     import ctypes as C
@@ -172,8 +173,11 @@ def test_exchange_plan_helpers_with_virtual_ranks(size):
     par = importlib.import_module("petsc-dev_b200.parallel")
     llp = C.POINTER(C.c_longlong)
     ip = C.POINTER(C.c_int)
-    N, nl, er, em = P.elements_tri2d(13, 9)
-    er = er.copy(); er[5] = -1                                  # an ignored id changes nothing about the routing of the rest
+    if mesh == "tri":
+        N, nl, er, em = P.elements_tri2d(13, 9)
+        er = er.copy(); er[5] = -1                              # an ignored id changes nothing about the routing of the rest
+    else:                                                       # random ids: elements that touch 1..4 ranks, repeats, ignored ids
+        N, nl, er, em = hostile_batch(7, m=97, ne=400, nl=4)
     ranges = np.ascontiguousarray(par.split_ownership(N, size), dtype=np.int32)
     parts = split_elements(er, em, nl, size)
     bufs, counts = [], np.zeros((size, size), np.int64)
