@@ -51,3 +51,23 @@ def test_no_device_fails_loudly():
     assert r.returncode != 0
     assert "Error in external library" in r.stderr and "No usable CUDA device" in r.stderr
     assert "KSP Residual norm" not in r.stdout
+
+
+def test_own_batch_driver_reference_arm_matches_the_ex4_golden():
+    """tests/c/batch_mpiaij.c (this repository's driver for MatSetValuesBatch on the parallel type) with the REFERENCE's
+    mpiaij type on the 3 x 3 grid must print the rows of the reference's golden ex4_0.out — the driver builds the same
+    elements as ex4.c, so the GPU test that compares the plugin arm with this arm is anchored to the golden too.  The
+    new KSP types and the batch ops are exported."""
+    _need()
+    exe = os.path.join(BIN, "b200_batch_mpiaij")
+    if not os.path.exists(exe):
+        pytest.skip("tests/c/batch_mpiaij.c not built")
+    r = subprocess.run([exe, "-X", "3", "-Y", "3", "-mat_type", "mpiaij"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr[-1000:]
+    gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_goldens.json")))["ksp_ex4_0"]["rows"]
+    want = [("row %d: %s" % (k, " ".join("(%d, %g) " % (c, v) for c, v in row))).strip() for k, row in enumerate(gold)]
+    got = [l.strip() for l in r.stdout.splitlines() if l.startswith("row ")]
+    assert got == want
+    lib = C.CDLL(PLUGIN, mode=C.RTLD_GLOBAL)
+    for s in ("KSPCreate_CGB200", "KSPCreate_GMRESB200", "MatB200GetHandle", "MatSeqAIJSetPreallocation_SeqAIJB200"):
+        assert hasattr(lib, s), s
