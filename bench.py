@@ -81,7 +81,7 @@ def _ref_slab_worker(rank, nprocs, nx, reps, warm, barrier, q):
     be).  All cores start together; returns the average seconds per MatMult on this core."""
     try:
         from oracle import refpetsc as R
-        P = importlib.import_module("petsc-dev_b200.problems")
+        P = importlib.import_module("workloads.problems")
         N = nx ** 3
         r0 = rank * (N // nprocs) + min(rank, N % nprocs)
         r1 = r0 + N // nprocs + (1 if rank < N % nprocs else 0)
@@ -132,7 +132,7 @@ def run_reference(args):
     if rank != 0:
         return
     from oracle import refpetsc as R
-    P = importlib.import_module("petsc-dev_b200.problems")
+    P = importlib.import_module("workloads.problems")
     nx = args.nx
     N = nx ** 3
     # all host cores first (forked before this process holds the big matrix)
@@ -171,7 +171,7 @@ def run_b200(args):
         args.gpus = world
     pb = importlib.import_module("petsc-dev_b200")
     par = importlib.import_module("petsc-dev_b200.parallel")
-    P = importlib.import_module("petsc-dev_b200.problems")
+    P = importlib.import_module("workloads.problems")
     dist = None
     if world > 1:
         import torch

@@ -27,7 +27,7 @@ def monitor_short(v):
 
 @pytest.fixture(scope="session")
 def P():
-    return importlib.import_module("petsc-dev_b200.problems")
+    return importlib.import_module("workloads.problems")
 
 
 @pytest.fixture(scope="session")

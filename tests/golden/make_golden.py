@@ -84,7 +84,7 @@ def main():
 
     # ---- oracle outputs on seeded inputs ----
     from oracle import refpetsc as R
-    P = importlib.import_module("petsc-dev_b200.problems")
+    P = importlib.import_module("workloads.problems")
     fx = {}
     n = 10007
     x, y, w = (P.random_vector(n, s) for s in (11, 12, 13))

@@ -25,7 +25,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", lrank))
     pb = importlib.import_module("petsc-dev_b200")
     par = importlib.import_module("petsc-dev_b200.parallel")
-    P = importlib.import_module("petsc-dev_b200.problems")
+    P = importlib.import_module("workloads.problems")
     pb.init(lrank)
     par.comm_init(rank, world, dist, device="cuda")
     if transport == "p2p":

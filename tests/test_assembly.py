@@ -9,7 +9,7 @@ import numpy as np
 import pytest
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-P = importlib.import_module("petsc-dev_b200.problems")
+P = importlib.import_module("workloads.problems")
 from oracle import assembly_restate as AR          # noqa: E402
 from oracle import refpetsc as R                   # noqa: E402
 

@@ -111,7 +111,7 @@ def _gloo_worker(rank, size, port, q):
     sys.path.insert(0, ROOT)
     import torch.distributed as td
     td.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=size)
-    P = importlib.import_module("petsc-dev_b200.problems")
+    P = importlib.import_module("workloads.problems")
     par = importlib.import_module("petsc-dev_b200.parallel")
     N = 12 ** 3
     ranges = par.split_ownership(N, size)

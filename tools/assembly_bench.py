@@ -11,7 +11,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 pb = importlib.import_module("petsc-dev_b200")
-P = importlib.import_module("petsc-dev_b200.problems")
+P = importlib.import_module("workloads.problems")
 argv = sys.argv[1:]
 def opt(name, default):
     return int(argv[argv.index(name) + 1]) if name in argv else default

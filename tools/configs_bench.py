@@ -11,7 +11,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 pb = importlib.import_module("petsc-dev_b200")
-P = importlib.import_module("petsc-dev_b200.problems")
+P = importlib.import_module("workloads.problems")
 pb.init(0)
 try:
     PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]

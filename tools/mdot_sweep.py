@@ -3,7 +3,7 @@
 import importlib, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-pb = importlib.import_module("petsc-dev_b200"); P = importlib.import_module("petsc-dev_b200.problems")
+pb = importlib.import_module("petsc-dev_b200"); P = importlib.import_module("workloads.problems")
 pb.init(0)
 n = 256 ** 3
 base = P.random_vector(n, 1)                    # one host vector for every buffer: bandwidth does not depend on the values

@@ -8,7 +8,7 @@ import torch, torch.distributed as dist
 rank, lrank, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
 torch.cuda.set_device(lrank)
 dist.init_process_group("nccl", device_id=torch.device("cuda", lrank))
-pb = importlib.import_module("petsc-dev_b200"); par = importlib.import_module("petsc-dev_b200.parallel"); P = importlib.import_module("petsc-dev_b200.problems")
+pb = importlib.import_module("petsc-dev_b200"); par = importlib.import_module("petsc-dev_b200.parallel"); P = importlib.import_module("workloads.problems")
 pb.init(lrank); par.comm_init(rank, world, dist, device="cuda")
 if (sys.argv[1] if len(sys.argv) > 1 else "p2p") == "p2p":
     par.enable_p2p()

@@ -4,7 +4,7 @@ import importlib, os, sys, time
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pb = importlib.import_module("petsc-dev_b200")
-P = importlib.import_module("petsc-dev_b200.problems")
+P = importlib.import_module("workloads.problems")
 pb.init(0)
 which = sys.argv[1:] or ["lap7", "s27", "plaw", "vec"]
 

@@ -5,7 +5,7 @@ import importlib, json, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pb = importlib.import_module("petsc-dev_b200")
-P = importlib.import_module("petsc-dev_b200.problems")
+P = importlib.import_module("workloads.problems")
 pb.init(0)
 n = 256 ** 3
 timed = "--time" in sys.argv

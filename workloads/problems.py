@@ -216,3 +216,8 @@ def elements_hex3d(nx, seed=11, scale_values=True):
     coef = 0.5 + u01(hash3(seed, np.arange(ne, dtype=np.uint64), 7)) if scale_values else np.ones(ne)
     mats = (coef[:, None] * base.reshape(1, 64)).reshape(-1)
     return nx ** 3, 8, rows, mats
+
+
+def random_vector_at(idx, seed, lo=-1.0, hi=1.0):
+    """Entries idx (global ids) of the vector random_vector(N, seed) — what a rank's ghost vector holds."""
+    return lo + (hi - lo) * u01(hash3(seed, np.asarray(idx, dtype=np.uint64), 0))
