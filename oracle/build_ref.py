@@ -55,6 +55,26 @@ HOT = ("src/mat/impls/aij/seq/aij.c", "src/mat/impls/aij/seq/inode.c", "src/mat/
        "src/vec/vec/utils/vpscat.c", "src/ksp/ksp/impls/cg/cg.c", "src/ksp/ksp/impls/gmres/")
 
 HAVE = {"PETSC_HAVE_MPIUNI", "PETSC_USE_LOG", "PETSC_HAVE_RAND", "PETSC_HAVE_DRAND48", "PETSC_USE_INFO"}  # packages we "have" for #requirespackage purposes
+MPIINC = os.path.join(REF, "include/mpiuni")       # where <mpi.h> comes from: the reference's one-rank MPIUNI ...
+MPIDEFS = []
+MPILIB = []                                        # ... whose mpi.c is compiled with the rest (src/sys/mpiuni)
+SHIM = os.path.join(os.path.dirname(HERE), "petsc-dev_b200", "mpishim")
+SHIMLIBDIR = os.path.join(os.path.dirname(HERE), "petsc-dev_b200", "lib")
+
+
+def use_mpi_shim():
+    """Second flavour of the same build: the SAME unmodified sources against the N-rank b200mpi subset
+    (petsc-dev_b200/mpishim) instead of MPIUNI -> oracle/_ref_mpi/libpetsc_ref_mpi.so.  Run with
+    petsc-dev_b200/lib/b200mpiexec -n P; this is the P > 1 oracle (real MatSetUpMultiply_MPIAIJ / VecScatterCreate_PtoS /
+    MatMult_MPIAIJ / KSPSolve on P ranks) and the all-cores CPU baseline of bench.py."""
+    global OUT, OBJ, LIB, HAVE, MPIINC, MPILIB, MPIDEFS
+    OUT = os.path.join(HERE, "_ref_mpi")
+    OBJ = os.path.join(OUT, "obj")
+    LIB = os.path.join(OUT, "libpetsc_ref_mpi.so")
+    HAVE = HAVE - {"PETSC_HAVE_MPIUNI"}
+    MPIINC = SHIM
+    MPIDEFS = ["-DPETSC_HAVE_MPI_TYPE_DUP", "-DPETSC_HAVE_MPI_FINALIZED"]   # what configure would have found
+    MPILIB = ["-L", SHIMLIBDIR, "-lb200mpi", "-Wl,-rpath,$ORIGIN/../../petsc-dev_b200/lib"]
 
 
 def parse_makefile(path):
@@ -106,8 +126,8 @@ def cflags(rel):
     # -ffp-contract=off: the reference's arithmetic is plain IEEE mul+add (no FMA contraction), so the
     # oracle is reproducible across x86 hosts with/without FMA units.
     return ["gcc", "-c", "-fPIC", opt, "-ffp-contract=off", "-fno-strict-aliasing", "-w", "-Werror=implicit-function-declaration",
-            "-I", CONF, "-I", os.path.join(REF, "include"), "-I", os.path.join(REF, "include/mpiuni"),
-            "-I", REF, "-D__SDIR__=\"%s/\"" % os.path.dirname(rel)]
+            "-I", CONF, "-I", os.path.join(REF, "include"), "-I", MPIINC,
+            "-I", REF, "-D__SDIR__=\"%s/\"" % os.path.dirname(rel)] + MPIDEFS
 
 
 def compile_one(rel):
@@ -116,7 +136,8 @@ def compile_one(rel):
     cmd = cflags(rel) + [src, "-o", obj]
     stamp = obj + ".cmd"
     key = hashlib.sha1((" ".join(cmd) + str(os.path.getmtime(src)) +
-                        "".join(str(os.path.getmtime(os.path.join(CONF, f))) for f in sorted(os.listdir(CONF)))
+                        "".join(str(os.path.getmtime(os.path.join(CONF, f))) for f in sorted(os.listdir(CONF))) +
+                        str(os.path.getmtime(os.path.join(MPIINC, "mpi.h")))
                         ).encode()).hexdigest()
     if os.path.exists(obj) and os.path.exists(stamp) and open(stamp).read() == key:
         return rel, obj, 0, ""
@@ -158,7 +179,7 @@ def main(verbose=True):
         obj = os.path.join(OBJ, name[:-2] + ".o")
         if (not os.path.exists(obj)) or os.path.getmtime(obj) < os.path.getmtime(src):
             cmd = ["gcc", "-c", "-fPIC", opt, "-ffp-contract=off", "-w", "-I", CONF,
-                   "-I", os.path.join(REF, "include"), "-I", os.path.join(REF, "include/mpiuni"), "-I", REF,
+                   "-I", os.path.join(REF, "include"), "-I", MPIINC, "-I", REF,
                    "-D__SDIR__=\"oracle/\"", src, "-o", obj]
             subprocess.run(cmd, check=True)
         extra.append(obj)
@@ -169,11 +190,13 @@ def main(verbose=True):
         return LIB
     rsp = os.path.join(OUT, "link.rsp")
     open(rsp, "w").write("\n".join(objs + extra))
-    subprocess.run(["gcc", "-shared", "-o", LIB, "@" + rsp, "-Wl,--no-undefined", "-lm", "-ldl"], check=True)
+    subprocess.run(["gcc", "-shared", "-o", LIB, "@" + rsp, "-Wl,--no-undefined", "-lm", "-ldl"] + MPILIB, check=True)
     if verbose:
         print("built", LIB)
     return LIB
 
 
 if __name__ == "__main__":
+    if "--mpi" in sys.argv:
+        use_mpi_shim()
     main()

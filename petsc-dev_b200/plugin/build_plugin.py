@@ -34,13 +34,86 @@ EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
 }
 
 
-def inc():
-    return ["-I", CONF, "-I", os.path.join(REF, "include"), "-I", os.path.join(REF, "include/mpiuni"), "-I", REF,
-            "-I", os.path.join(ROOT, "include")]
+MPI_EXAMPLES = {  # additional unmodified reference programs whose goldens need more than one rank (built in the MPI flavour only)
+    "vec_ex4": "src/vec/vec/examples/tests/ex4.c", "vec_ex9": "src/vec/vec/examples/tests/ex9.c",
+    "vec_ex11": "src/vec/vec/examples/tests/ex11.c", "vec_ex12": "src/vec/vec/examples/tests/ex12.c",
+    "vec_ex13": "src/vec/vec/examples/tests/ex13.c", "vec_ex14": "src/vec/vec/examples/tests/ex14.c",
+    "vec_ex17": "src/vec/vec/examples/tests/ex17.c", "vec_ex22": "src/vec/vec/examples/tests/ex22.c",
+    "vec_ex23": "src/vec/vec/examples/tests/ex23.c", "vec_ex24": "src/vec/vec/examples/tests/ex24.c",
+    "vec_ex25": "src/vec/vec/examples/tests/ex25.c", "vec_ex33": "src/vec/vec/examples/tests/ex33.c",
+    "vec_ex5": "src/vec/vec/examples/tests/ex5.c", "vec_ex10": "src/vec/vec/examples/tests/ex10.c",
+    "vec_ex3": "src/vec/vec/examples/tests/ex3.c", "vec_ex1": "src/vec/vec/examples/tests/ex1.c",
+    # this repository's own programs (public PETSc API only)
+    "b200_dump_mpiaij": os.path.join(ROOT, "tests", "c", "dump_mpiaij.c"),
+    "b200_ref_bench": os.path.join(ROOT, "oracle", "ref_bench.c"),
+    "mpishim_selftest": os.path.join(ROOT, "tests", "c", "mpishim_selftest.c"),
+}
+
+SHIM = os.path.join(ROOT, "petsc-dev_b200", "mpishim")
+
+# the two PETSc builds a plugin can be made for on this box: the reference against its own one-rank MPIUNI, and the same
+# sources against the N-rank b200mpi subset (oracle/build_ref.py --mpi), run with petsc-dev_b200/lib/b200mpiexec -n P
+FLAVOURS = {
+    "uni": dict(refdir=os.path.join(ROOT, "oracle", "_ref"), reflib="petsc_ref", mpiinc=os.path.join(REF, "include/mpiuni"),
+                plugdir=LIBDIR, extra_libs=[], rpaths=["$ORIGIN", "$ORIGIN/../../oracle/_ref"], defs=[]),
+    "mpi": dict(refdir=os.path.join(ROOT, "oracle", "_ref_mpi"), reflib="petsc_ref_mpi", mpiinc=SHIM,
+                plugdir=os.path.join(LIBDIR, "mpi"), extra_libs=["-lb200mpi"],
+                rpaths=["$ORIGIN/..", "$ORIGIN/../../../oracle/_ref_mpi"], defs=["-DPETSC_HAVE_MPI_TYPE_DUP", "-DPETSC_HAVE_MPI_FINALIZED"]),
+}
+
+
+def inc(fl):
+    return ["-I", CONF, "-I", os.path.join(REF, "include"), "-I", fl["mpiinc"], "-I", REF, "-I", os.path.join(ROOT, "include")] + fl["defs"]
 
 
 def newer(out, srcs):
     return (not os.path.exists(out)) or any(os.path.getmtime(s) > os.path.getmtime(out) for s in srcs if os.path.exists(s))
+
+
+def build_flavour(name, verbose=True):
+    fl = FLAVOURS[name]
+    reflib = os.path.join(fl["refdir"], "lib%s.so" % fl["reflib"])
+    plugin = os.path.join(fl["plugdir"], "libpetscb200plugin.so")
+    bindir = os.path.join(fl["refdir"], "bin")
+    if not os.path.exists(reflib):
+        if name == "uni":
+            raise SystemExit("build oracle/_ref/libpetsc_ref.so first (oracle/build_ref.py)")
+        if verbose:
+            print("skipping the %s flavour: %s not built (oracle/build_ref.py --mpi)" % (name, reflib))
+        return plugin
+    os.makedirs(fl["plugdir"], exist_ok=True)
+    os.makedirs(bindir, exist_ok=True)
+    srcs = [os.path.join(HERE, f) for f in ("b200vec.c", "b200mat.c", "b200ksp.c", "b200reg.c", "b200scatter.c")]
+    srcs = [f for f in srcs if os.path.exists(f)]
+    deps = srcs + [os.path.join(HERE, "petscb200plugin.h"), os.path.join(ROOT, "include", "petscb200.h"),
+                   os.path.join(CONF, "petscconf.h"), os.path.join(fl["mpiinc"], "mpi.h")]
+    rp = ["-Wl,-rpath," + r for r in fl["rpaths"]]
+    if newer(plugin, deps):
+        cmd = ["gcc", "-shared", "-fPIC", "-O2", "-g", "-w",
+               "-ffp-contract=off", "-D__INSDIR__=petsc-dev_b200/plugin/"] + inc(fl) + srcs + \
+              ["-o", plugin, "-L", LIBDIR, "-lpetscb200", "-L", fl["refdir"], "-l" + fl["reflib"]] + fl["extra_libs"] + rp + \
+              ["-Wl,--no-undefined", "-lm"]
+        subprocess.run(cmd, check=True)
+        if verbose:
+            print("built", plugin)
+    examples = dict(EXAMPLES)
+    if name == "mpi":
+        examples.update(MPI_EXAMPLES)
+    for prog, rel in examples.items():
+        src = os.path.join(REF, rel)
+        out = os.path.join(bindir, prog)
+        if not os.path.exists(src):
+            continue
+        if newer(out, [src, reflib]):
+            cmd = ["gcc", "-O1", "-w", "-D__INSDIR__=%s/" % os.path.dirname(rel)] + inc(fl) + [src, "-o", out,
+                   "-L", fl["refdir"], "-l" + fl["reflib"], "-L", LIBDIR] + fl["extra_libs"] + \
+                  ["-Wl,-rpath,$ORIGIN/..", "-Wl,-rpath,$ORIGIN/../../../petsc-dev_b200/lib", "-Wl,--export-dynamic", "-lm", "-ldl"]
+            r = subprocess.run(cmd, capture_output=True, text=True)
+            if r.returncode:
+                print("example %s failed to build:\n%s" % (prog, r.stderr[-1500:]), file=sys.stderr)
+            elif verbose:
+                print("built", out)
+    return plugin
 
 
 def main(verbose=True):
@@ -48,34 +121,8 @@ def main(verbose=True):
         if verbose:
             print("reference headers absent; prebuilt plugin:", PLUGIN, os.path.exists(PLUGIN))
         return PLUGIN
-    if not os.path.exists(os.path.join(REFLIBDIR, "libpetsc_ref.so")):
-        raise SystemExit("build oracle/_ref/libpetsc_ref.so first (oracle/build_ref.py)")
-    os.makedirs(LIBDIR, exist_ok=True)
-    os.makedirs(BINDIR, exist_ok=True)
-    srcs = [os.path.join(HERE, f) for f in ("b200vec.c", "b200mat.c", "b200ksp.c", "b200reg.c")]
-    deps = srcs + [os.path.join(HERE, "petscb200plugin.h"), os.path.join(ROOT, "include", "petscb200.h"),
-                   os.path.join(CONF, "petscconf.h")]
-    if newer(PLUGIN, deps):
-        cmd = ["gcc", "-shared", "-fPIC", "-O2", "-g", "-w",
-               "-ffp-contract=off", "-D__INSDIR__=petsc-dev_b200/plugin/"] + inc() + srcs + \
-              ["-o", PLUGIN, "-L", LIBDIR, "-lpetscb200", "-L", REFLIBDIR, "-lpetsc_ref",
-               "-Wl,-rpath,$ORIGIN", "-Wl,-rpath,$ORIGIN/../../oracle/_ref", "-Wl,--no-undefined", "-lm"]
-        subprocess.run(cmd, check=True)
-        if verbose:
-            print("built", PLUGIN)
-    for name, rel in EXAMPLES.items():
-        src = os.path.join(REF, rel)
-        out = os.path.join(BINDIR, name)
-        if not os.path.exists(src):
-            continue
-        if newer(out, [src, os.path.join(REFLIBDIR, "libpetsc_ref.so")]):
-            cmd = ["gcc", "-O1", "-w", "-D__INSDIR__=%s/" % os.path.dirname(rel)] + inc() + [src, "-o", out,
-                   "-L", REFLIBDIR, "-lpetsc_ref", "-Wl,-rpath,$ORIGIN/..", "-Wl,--export-dynamic", "-lm", "-ldl"]
-            r = subprocess.run(cmd, capture_output=True, text=True)
-            if r.returncode:
-                print("example %s failed to build:\n%s" % (name, r.stderr[-1500:]), file=sys.stderr)
-            elif verbose:
-                print("built", out)
+    build_flavour("uni", verbose)
+    build_flavour("mpi", verbose)
     return PLUGIN
 
 
