@@ -6,7 +6,7 @@ T=$1; shift
 for i in $(seq 1 40); do
   /usr/local/graft/bin/gpurun $G --timeout $T -- "$@"
   rc=$?
-  if [ $rc -ne 3 ]; then exit $rc; fi
+  if [ $rc -ne 3 ] && [ $rc -ne 2 ]; then exit $rc; fi
   sleep 120
 done
 exit 3
