@@ -6,6 +6,7 @@
  * B200MPI_RING_KB (default: 4 MiB for P <= 16, shrinking so that the P*P rings stay within 1 GiB of address space). */
 #define _GNU_SOURCE
 #include <errno.h>
+#include <sched.h>
 #include <signal.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -63,11 +64,22 @@ int main(int argc, char **argv)
   snprintf(buf, sizeof(buf), "%d", fd); setenv("B200MPI_FD", buf, 1);
   fflush(stdout); fflush(stderr);
   g_n = n;
+  /* one core per rank when there are enough of them (B200MPI_BIND=0 switches the binding off): spinning ranks that migrate
+   * between cores pay for it in every message */
+  cpu_set_t allowed;
+  int ncpu = 0, cpus[CPU_SETSIZE], bind = 1;
+  const char *eb = getenv("B200MPI_BIND");
+  if (eb && !atoi(eb)) bind = 0;
+  CPU_ZERO(&allowed);
+  if (sched_getaffinity(0, sizeof(allowed), &allowed) == 0)
+    for (int c = 0; c < CPU_SETSIZE; c++) if (CPU_ISSET(c, &allowed)) cpus[ncpu++] = c;
+  if (ncpu < n) bind = 0;
   for (int r = 0; r < n; r++) {
     pid_t p = fork();
     if (p < 0) { perror("b200mpiexec: fork"); kill_all(SIGTERM); return 2; }
     if (p == 0) {
       snprintf(buf, sizeof(buf), "%d", r); setenv("B200MPI_RANK", buf, 1);
+      if (bind) { cpu_set_t one; CPU_ZERO(&one); CPU_SET(cpus[(size_t)r * ncpu / n], &one); sched_setaffinity(0, sizeof(one), &one); }
       execvp(argv[a], argv + a);
       fprintf(stderr, "b200mpiexec: cannot run %s: %s\n", argv[a], strerror(errno));
       _exit(127);
