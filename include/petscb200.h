@@ -104,7 +104,8 @@ int b200_comm_destroy(void);
 int b200_comm_allreduce_sum(double *dvals, int n);              /* in place, device buffer, stream-ordered        */
 int b200_comm_barrier(void);
 /* peer-memory mode: reductions and the ghost exchange go through NVLink peer stores instead of NCCL */
-int b200_comm_enable_p2p(int enable);
+int b200_comm_enable_p2p(int enable);      /* 1: on (size > 1).  2: also on a ONE-rank communicator ("loop-back": the rank is its own
+                                              neighbour; the same kernels, flags and credits, stores stay on the device — single-GPU tests) */
 int b200_comm_p2p_enabled(int *enabled);
 
 /* ---- Vec kernels (device arrays of n doubles) ----------------------------------------------------------------
@@ -243,6 +244,9 @@ int b200_mat_create_mpiaij(int m, int n_local, int N,
                            int nfrom, const int *from_procs, const int *from_starts,
                            b200_mat *A);
 int b200_mat_mult_phases(b200_mat A, const double *x, double *y, double *ms4_host);  /* diagnostic: device ms of exchange-begin | diagonal | exchange-end | off-diagonal */
+/* 1 when MatMult/MatMultAdd of this operator run as ONE kernel (ghost exchange, diagonal and off-diagonal block fused:
+ * peer-memory transport, thin off-diagonal block, no long rows); B200_MPI_FUSED=0 in the environment keeps the four-step path */
+int b200_mat_mpiaij_is_fused(b200_mat A, int *fused, int *boundary_tiles);
 int b200_mat_mpiaij_get_lvec(b200_mat A, double **lvec, int *nghost);         /* Mat_MPIAIJ::lvec, mpiaij.h:60   */
 int b200_mat_mpiaij_scatter(b200_mat A, const double *x);                     /* VecScatterBegin+End only        */
 int b200_mat_mpiaij_set_lvec(b200_mat A, const double *ghost_values_dev);     /* caller-performed scatter (P virtual ranks in one process) */

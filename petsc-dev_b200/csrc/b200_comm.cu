@@ -29,6 +29,7 @@
 #include <vector>
 #include <algorithm>
 #include "b200_p2p_dev.cuh"
+#include "b200_spmv_mpi_kernels.cuh"
 
 struct NcclApi {
   void *h;
@@ -197,8 +198,8 @@ extern "C" int b200_comm_enable_p2p(int enable)
     return 0;
   }
   if (c.p2p) return 0;
-  if (c.size <= 1) return 0;
-  if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "b200_comm_enable_p2p needs b200_comm_init first (the handles travel over it)");
+  if (c.size <= 1 && enable != 2) return 0;
+  if (c.size > 1 && !c.nccl) return b200_seterr(B200_ERR_ORDER, "b200_comm_enable_p2p needs b200_comm_init first (the handles travel over it)");
   B200P2P *P = (B200P2P *)calloc(1, sizeof(B200P2P));
   if (!P) return b200_seterr(B200_ERR_MEM, "out of host memory");
   size_t mb = 512;
@@ -208,6 +209,16 @@ extern "C" int b200_comm_enable_p2p(int enable)
   B200_CUDA(cudaMalloc((void **)&P->arena, P->bytes));
   B200_CUDA(cudaMemset(P->arena, 0, P->bytes));
   P->bump = P2P_CTRL_BYTES;
+  if (c.size <= 1) {
+    /* loop-back (enable == 2): one rank whose only peer is itself.  The exchange kernels, flags and credits run exactly
+     * as between GPUs, only the stores stay on this device — the single-GPU test of the multi-GPU path */
+    unsigned long long *tab[1] = {reinterpret_cast<unsigned long long *>(P->arena)};
+    P->peer[0] = P->arena;
+    B200_CUDA(cudaMalloc((void **)&P->d_inbox, sizeof(tab)));
+    B200_CUDA(cudaMemcpy(P->d_inbox, tab, sizeof(tab), cudaMemcpyHostToDevice));
+    c.peer = P; c.p2p = true;
+    return 0;
+  }
   /* exchange the IPC handles through the NCCL communicator */
   cudaIpcMemHandle_t mine, all[B200_MAX_RANKS];
   B200_CUDA(cudaIpcGetMemHandle(&mine, P->arena));
@@ -286,16 +297,6 @@ __global__ void __launch_bounds__(256) pack_kernel(int n, const int *__restrict_
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) buf[i] = __ldg(&x[__ldg(&idx[i])]);
 }
 
-/* per-matrix peer plan: where this rank's packed entries go on each neighbour, and the flags/credits around them */
-struct PeerPlanDev {
-  int nto, nfrom;
-  const int *to_starts;                          /* [nto+1]                                                          */
-  double *const *dst;                            /* [2][nto]: neighbour k's ghost-vector window for me, per parity   */
-  unsigned long long *const *rflag;              /* [nto]  arrival flag on neighbour k (its flag[my rank])           */
-  const unsigned long long *const *lcredit;      /* [nto]  local credit written by neighbour k (consumed exchange)   */
-  unsigned long long *const *rcredit;            /* [nfrom] credit slot on sender k (its credit[my rank])            */
-  const unsigned long long *const *lflag;        /* [nfrom] local arrival flag written by sender k                   */
-};
 struct PeerPlan {
   PeerPlanDev dev;                               /* forward: x -> neighbours' ghost vectors (MatMult)                */
   PeerPlanDev rev;                               /* reverse: my ghost contributions -> their owners (MatMultTranspose) */
@@ -353,6 +354,8 @@ __global__ void __launch_bounds__(32) wait_arrivals_kernel(const PeerPlanDev pla
 {
   if ((int)threadIdx.x < plan.nfrom) { const long long t0 = clock64(); while (ld_acquire_sys(plan.lflag[threadIdx.x]) < epoch) b200_spin_guard(t0); }
 }
+
+static int fusedplan_build(b200_mat M, const int *Bi);
 
 static void peerplan_free(b200_mat M)
 {
@@ -420,13 +423,16 @@ static int peerplan_build(b200_mat M)
   for (int r = 0; r < 2 * R; r++) mine[RECV0 + r] = -1;
   for (int k = 0; k < nfrom; k++) mine[RECV0 + M->from_procs[k]] = M->from_starts[k];
   for (int k = 0; k < nto; k++)   mine[RECV0 + R + M->to_procs[k]] = M->to_starts[k];
-  long long *dm = NULL;
-  B200_CUDA(cudaMalloc((void **)&dm, sizeof(long long) * (size_t)W * (size_t)(size + 1)));
-  B200_CUDA(cudaMemcpy(dm, mine, sizeof(mine), cudaMemcpyHostToDevice));
-  B200_NCCL(g_nccl.AllGather(dm, dm + W, (size_t)W, ncclInt64, (ncclComm_t)c.nccl, c.stream));
-  B200_CUDA(cudaStreamSynchronize(c.stream));
-  B200_CUDA(cudaMemcpy(all, dm + W, sizeof(long long) * (size_t)W * (size_t)size, cudaMemcpyDeviceToHost));
-  cudaFree(dm);
+  if (size == 1) memcpy(all[0], mine, sizeof(mine));
+  else {
+    long long *dm = NULL;
+    B200_CUDA(cudaMalloc((void **)&dm, sizeof(long long) * (size_t)W * (size_t)(size + 1)));
+    B200_CUDA(cudaMemcpy(dm, mine, sizeof(mine), cudaMemcpyHostToDevice));
+    B200_NCCL(g_nccl.AllGather(dm, dm + W, (size_t)W, ncclInt64, (ncclComm_t)c.nccl, c.stream));
+    B200_CUDA(cudaStreamSynchronize(c.stream));
+    B200_CUDA(cudaMemcpy(all, dm + W, sizeof(long long) * (size_t)W * (size_t)size, cudaMemcpyDeviceToHost));
+    cudaFree(dm);
+  }
   bool ok = true;
   for (int r = 0; r < size; r++) ok = ok && all[r][OK] == 1;
   if (!ok) { P->bump = lo; return 1; }                            /* every rank sees the same table -> same decision  */
@@ -512,7 +518,7 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
   const int nsend = M->to_starts[nto];
   if (M->from_starts[nfrom] != nghost) { b200_mat_destroy(M); return b200_seterr(B200_ERR_ARG_SIZ, "receive lists cover %d of %d ghosts", M->from_starts[nfrom], nghost); }
   B200_CUDA(cudaMalloc((void **)&M->d_garray, sizeof(int) * (size_t)(nghost + 1)));
-  if (g_b200.p2p && g_b200.size > 1) {
+  if (g_b200.p2p && (g_b200.size > 1 || nto + nfrom > 0)) {
     /* collective; falls back to the NCCL exchange for this matrix (on every rank alike) when an arena is full */
     const int prc = peerplan_build(M);
     if (prc > 1) { b200_mat_destroy(M); return prc; }
@@ -528,7 +534,155 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
   if (nghost) B200_CUDA(cudaMemcpy(M->d_garray, garray, sizeof(int) * (size_t)nghost, cudaMemcpyHostToDevice));
   if (nsend) B200_CUDA(cudaMemcpy(M->d_to_indices, to_indices, sizeof(int) * (size_t)nsend, cudaMemcpyHostToDevice));
   M->epoch = 0;
+  if (M->peerplan) { rc = fusedplan_build(M, Bi); if (rc) { b200_mat_destroy(M); return rc; } }
   *Aout = M;
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------ one-launch MatMult */
+struct FusedPlan {
+  int    ntiles, grid, nboundary, threads, tile_nnz;
+  int4  *d_tiles;
+  int   *d_flag;
+  double *d_dotpart;
+};
+
+void b200_mpiaij_fused_free(b200_mat M)
+{
+  FusedPlan *fp = (FusedPlan *)M->fusedplan;
+  if (!fp) return;
+  cudaFree(fp->d_tiles); cudaFree(fp->d_flag); cudaFree(fp->d_dotpart);
+  free(fp);
+  M->fusedplan = NULL;
+}
+
+bool b200_mpiaij_fused(b200_mat A) { return A && A->fusedplan != NULL; }
+
+void b200_mpiaij_fused_dotparts(b200_mat A, const double **p, int *n)
+{
+  FusedPlan *fp = (FusedPlan *)A->fusedplan;
+  *p = fp->d_dotpart; *n = fp->grid;
+}
+
+typedef void (*fused_kern_t)(const MpiSpmvArgs);
+template <int G, int MINB> static fused_kern_t fused_pick(bool add, bool dot)
+{
+  if (add) return dot ? spmv_mpiaij_kernel<G, true, true, 256, 2048, MINB> : spmv_mpiaij_kernel<G, true, false, 256, 2048, MINB>;
+  return dot ? spmv_mpiaij_kernel<G, false, true, 256, 2048, MINB> : spmv_mpiaij_kernel<G, false, false, 256, 2048, MINB>;
+}
+static int g_fused_minb = -1;
+static fused_kern_t fused_kernel(int G, bool add, bool dot)
+{
+  if (g_fused_minb < 0) { const char *e = getenv("B200_MPI_FUSED_OCC8"); g_fused_minb = (e && !atoi(e)) ? 1 : 8; }
+  switch (G) {
+    case 1:  return g_fused_minb == 8 ? fused_pick<1, 8>(add, dot) : fused_pick<1, 1>(add, dot);
+    case 2:  return fused_pick<2, 1>(add, dot);
+    case 4:  return fused_pick<4, 1>(add, dot);
+    case 8:  return fused_pick<8, 1>(add, dot);
+    case 16: return fused_pick<16, 1>(add, dot);
+    default: return fused_pick<32, 1>(add, dot);
+  }
+}
+
+/* Decide whether this operator takes the one-launch path and, if so, lay out its tile table: the diagonal block's row
+ * tiles, those without off-diagonal entries first.  Bi = host row offsets of the off-diagonal block. */
+static int fusedplan_build(b200_mat M, const int *Bi)
+{
+  const B200Seq *A = &M->A, *B = &M->B;
+  const char *e = getenv("B200_MPI_FUSED");
+  if (e && !atoi(e)) return 0;
+  if (!M->peerplan || A->m == 0 || A->ntiles == 0) return 0;
+  if (A->nlong || A->compressed || A->nstrips > 1 || B->nstrips > 1 || A->cfg != 0 || A->park) return 0;
+  if (A->m != A->n) return 0;
+  if (B->nz * 4 > A->nz) return 0;                         /* a fat off-diagonal block streams better through its own TMA pipeline */
+  std::vector<int4> tiles((size_t)A->ntiles), sorted;
+  std::vector<int>  flag;
+  B200_CUDA(cudaMemcpy(tiles.data(), A->d_tiles, sizeof(int4) * (size_t)A->ntiles, cudaMemcpyDeviceToHost));
+  sorted.reserve(tiles.size()); flag.reserve(tiles.size());
+  int nb = 0;
+  for (int pass = 0; pass < 2; pass++)
+    for (size_t t = 0; t < tiles.size(); t++) {
+      if (tiles[t].y < 0) return 0;                        /* chunk of a long row: not on this path */
+      const int f = Bi[tiles[t].y] > Bi[tiles[t].x];
+      if (f == pass) { int4 d = tiles[t]; if (f) d.z |= (int)0x80000000; sorted.push_back(d); flag.push_back(f); nb += f; }
+    }
+  FusedPlan *fp = (FusedPlan *)calloc(1, sizeof(FusedPlan));
+  if (!fp) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  fp->ntiles = A->ntiles; fp->nboundary = nb; fp->threads = 256; fp->tile_nnz = 2048;
+  const size_t smem = SpmvSmem<256, 2048, 1>::BYTES;
+  int occ = 0;
+  for (int add = 0; add < 2; add++) for (int dot = 0; dot < 2; dot++) {
+    fused_kern_t k = fused_kernel(A->G, add, dot);
+    B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int o = 0;
+    B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, k, 256, smem));
+    if (!occ || o < occ) occ = o;
+  }
+  if (occ < 1) { free(fp); return 0; }
+  /* every CTA of the grid is resident at once (waits on arrival flags never hold up a CTA that still has to send) */
+  fp->grid = g_b200.nsm * occ;
+  if (fp->grid > fp->ntiles) fp->grid = fp->ntiles;
+  B200_CUDA(cudaMalloc((void **)&fp->d_tiles, sizeof(int4) * sorted.size()));
+  B200_CUDA(cudaMemcpy(fp->d_tiles, sorted.data(), sizeof(int4) * sorted.size(), cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMalloc((void **)&fp->d_flag, sizeof(int) * flag.size()));
+  B200_CUDA(cudaMemcpy(fp->d_flag, flag.data(), sizeof(int) * flag.size(), cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMalloc((void **)&fp->d_dotpart, sizeof(double) * (size_t)(fp->grid + 1)));
+  M->fusedplan = fp;
+  return 0;
+}
+
+extern "C" int b200_mat_mpiaij_is_fused(b200_mat A, int *fused, int *boundary_tiles)
+{
+  if (!A || A->kind != 1) return b200_seterr(B200_ERR_ARG_WRONG, "not an MPIAIJ matrix");
+  if (fused) *fused = A->fusedplan ? 1 : 0;
+  if (boundary_tiles) *boundary_tiles = A->fusedplan ? ((FusedPlan *)A->fusedplan)->nboundary : 0;
+  return 0;
+}
+
+/* z = (add ? yin : 0) + A_d x + B ghost(x), exchange included, in ONE launch.  want_dot: per-CTA partials of x . (z - yin)
+ * are left for the caller (b200_mpiaij_fused_dotparts). */
+int b200_mpiaij_mult_fused(b200_mat M, const double *x, const double *yin, double *z, bool add, bool want_dot)
+{
+  B200Ctx &c = g_b200;
+  FusedPlan *fp = (FusedPlan *)M->fusedplan;
+  PeerPlan *pp = (PeerPlan *)M->peerplan;
+  M->epoch++;
+  MpiSpmvArgs a;
+  memset(&a, 0, sizeof(a));
+  a.ntiles = fp->ntiles; a.tiles = fp->d_tiles;
+  a.ai = M->A.d_i; a.aj = M->A.d_j; a.aa = M->A.d_a;
+  a.bi = M->B.d_i; a.bj = M->B.d_j; a.ba = M->B.d_a;
+  a.x = x; a.yin = yin; a.z = z;
+  a.lvec = M->d_lvec[M->epoch & 1];
+  a.dotpart = fp->d_dotpart; a.dotx = x;
+  a.nsend = M->to_starts[M->nto];
+  a.npack = (M->nto + M->nfrom) ? (a.nsend + fp->threads - 1) / fp->threads : 0;
+  if ((M->nto + M->nfrom) && a.npack < 1) a.npack = 1;
+  if (a.npack > fp->grid) a.npack = fp->grid;
+  a.to_idx = M->d_to_indices;
+  a.plan = pp->dev;
+  a.parity = (int)(M->epoch & 1); a.epoch = (unsigned long long)M->epoch; a.ticket = pp->d_ticket;
+  fused_kernel(M->A.G, add, want_dot)<<<fp->grid, fp->threads, SpmvSmem<256, 2048, 1>::BYTES, c.stream>>>(a);
+  B200_LAUNCHED(1);
+  return 0;
+}
+
+/* MatMult_MPIAIJ / MatMultAdd_MPIAIJ (mpiaij.c:1102-1143) */
+int b200_mpiaij_mult(b200_mat A, const double *x, const double *yin, double *z, bool add)
+{
+  B200Ctx &c = g_b200;
+  if (c.multi_stream) {                                   /* a caller that alternates streams: products of one matrix stay ordered */
+    if (!A->ev_done) B200_CUDA(cudaEventCreateWithFlags(&A->ev_done, cudaEventDisableTiming));
+    if (A->last_stream && A->last_stream != c.stream) B200_CUDA(cudaStreamWaitEvent(c.stream, A->ev_done, 0));
+  }
+  if (A->fusedplan) { B200_CHK(b200_mpiaij_mult_fused(A, x, yin, z, add, false)); }
+  else {
+    B200_CHK(b200_mpiaij_exchange_begin(A, x));
+    B200_CHK(b200_seq_mult(&A->A, x, yin, z, add, NULL));
+    B200_CHK(b200_mpiaij_exchange_end(A));
+    B200_CHK(b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], z, z, true, NULL));
+  }
+  if (c.multi_stream) { B200_CUDA(cudaEventRecord(A->ev_done, c.stream)); A->last_stream = c.stream; }
   return 0;
 }
 
@@ -556,8 +710,8 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x)
 {
   B200Ctx &c = g_b200;
   A->epoch++;
-  if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
-  if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "MPIAIJ MatMult on %d ranks needs b200_comm_init", c.size);
+  if ((c.size <= 1 && !A->peerplan) || (A->nto == 0 && A->nfrom == 0)) return 0;
+  if (!c.nccl && !A->peerplan) return b200_seterr(B200_ERR_ORDER, "MPIAIJ MatMult on %d ranks needs b200_comm_init", c.size);
   const int nsend = A->to_starts[A->nto];
   double *lvec = A->d_lvec[A->epoch & 1];
   if (A->peerplan) {
@@ -593,7 +747,7 @@ int b200_mpiaij_exchange_begin(b200_mat A, const double *x)
 int b200_mpiaij_exchange_end(b200_mat A)
 {
   B200Ctx &c = g_b200;
-  if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
+  if ((c.size <= 1 && !A->peerplan) || (A->nto == 0 && A->nfrom == 0)) return 0;
   if (A->peerplan) {
     B200_CUDA(cudaStreamWaitEvent(c.stream, c.ev_join, 0));        /* x may be overwritten only after the pack kernel read it */
     if (A->nfrom) {
@@ -632,8 +786,8 @@ static int reverse_begin(b200_mat A, const double *ghost_values, const double **
   const int nghost = A->nghost, nto = A->nto, nfrom = A->nfrom;
   *buf_out = A->d_sendbuf;
   A->repoch++;
-  if (c.size <= 1 || (nto == 0 && nfrom == 0)) return 0;
-  if (!c.nccl) return b200_seterr(B200_ERR_ORDER, "a reverse ghost exchange on %d ranks needs b200_comm_init", c.size);
+  if ((c.size <= 1 && !A->peerplan) || (nto == 0 && nfrom == 0)) return 0;
+  if (!c.nccl && !A->peerplan) return b200_seterr(B200_ERR_ORDER, "a reverse ghost exchange on %d ranks needs b200_comm_init", c.size);
   if (A->peerplan) {
     PeerPlan *pp = (PeerPlan *)A->peerplan;
     int g = (nghost + 1023) / 1024; if (g > B200_NSM * 2) g = B200_NSM * 2; if (g < 1) g = 1;
@@ -658,7 +812,7 @@ static int reverse_begin(b200_mat A, const double *ghost_values, const double **
 static int reverse_wait(b200_mat A)
 {
   B200Ctx &c = g_b200;
-  if (c.size <= 1 || (A->nto == 0 && A->nfrom == 0)) return 0;
+  if ((c.size <= 1 && !A->peerplan) || (A->nto == 0 && A->nfrom == 0)) return 0;
   if (A->peerplan) {
     if (A->nto) {
       wait_arrivals_kernel<<<1, 32, 0, c.stream>>>(((PeerPlan *)A->peerplan)->rev, (unsigned long long)A->repoch);
@@ -690,7 +844,7 @@ int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, do
   if (A->A.m == 0) { if (yin && z != yin && A->A.n > 0) B200_CHK(b200_vec_copy(A->A.n, yin, z)); }
   else if (yin) { B200_CHK(b200_seq_mult(A->A.T, x, yin, z, true, NULL)); }
   else { B200_CHK(b200_seq_mult(A->A.T, x, NULL, z, false, NULL)); }
-  if (c.size <= 1) return 0;
+  if (c.size <= 1 && !A->peerplan) return 0;
   B200_CHK(reverse_wait(A));
   for (int k = 0; k < nto; k++) {
     const int len = A->to_starts[k + 1] - A->to_starts[k];
@@ -825,10 +979,10 @@ extern "C" int b200_scatter_end(b200_scatter S, double *x, double *y, int add, i
   b200_mat E = S->ex;
   if (!reverse) {
     B200_CHK(b200_mpiaij_exchange_end(E));
-    if (g_b200.size <= 1) return 0;
+    if (g_b200.size <= 1 && !E->peerplan) return 0;
     return scatter_store(S->nrecv, S->d_from_indices, NULL, E->d_lvec[E->epoch & 1], y, add != 0, S->dup_from);
   }
-  if (g_b200.size <= 1) return 0;
+  if (g_b200.size <= 1 && !E->peerplan) return 0;
   B200_CHK(reverse_wait(E));
   const double *buf = E->peerplan ? ((PeerPlan *)E->peerplan)->rbuf[E->repoch & 1] : E->d_sendbuf;
   for (int k = 0; k < E->nto; k++) {                      /* neighbour by neighbour, ascending rank: fixed summation order */

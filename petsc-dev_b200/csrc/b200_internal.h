@@ -41,6 +41,7 @@ struct B200Ctx {
   void        *nccl;         /* ncclComm_t                                                                         */
   bool         p2p;
   B200P2P     *peer;
+  bool         multi_stream;  /* the caller has handed in a stream of its own at least once (b200_set_stream)          */
 };
 
 extern B200Ctx g_b200;
@@ -106,6 +107,9 @@ struct b200_mat_s {
   double  *d_ghost_t;         /* [nghost] B^T x, what this rank contributes to rows its neighbours own                */
   void    *peerplan;          /* per-matrix peer-store plan (b200_comm.cu)                                            */
   void    *batchplan;         /* element -> nonzero plan kept by the device assembly (b200_assembly.cu), or NULL       */
+  void    *fusedplan;         /* one-launch MatMult (exchange + both blocks in one kernel, b200_comm.cu), or NULL      */
+  cudaEvent_t  ev_done;       /* end of the last product, for callers that alternate between streams                   */
+  cudaStream_t last_stream;
 };
 
 int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
@@ -116,6 +120,11 @@ int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doub
 int  b200_seq_transpose(B200Seq *S);
 void b200_seq_dotparts(const B200Seq *S, const double **p, int *n);
 int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out);
+int  b200_mpiaij_mult(b200_mat A, const double *x, const double *yin, double *z, bool add);   /* MatMult / MatMultAdd of the parallel type */
+bool b200_mpiaij_fused(b200_mat A);
+int  b200_mpiaij_mult_fused(b200_mat A, const double *x, const double *yin, double *z, bool add, bool want_dot);
+void b200_mpiaij_fused_dotparts(b200_mat A, const double **p, int *n);
+void b200_mpiaij_fused_free(b200_mat A);
 
 /* internal cross-file entry points */
 int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_max /*0 sum, 1 max*/);

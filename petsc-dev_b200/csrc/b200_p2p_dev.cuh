@@ -25,6 +25,17 @@ __device__ __forceinline__ double ld_relaxed_sys_f64(const double *p)
   return v;
 }
 
+/* per-matrix peer plan: where this rank's packed entries go on each neighbour, and the flags/credits around them */
+struct PeerPlanDev {
+  int nto, nfrom;
+  const int *to_starts;                          /* [nto+1]                                                          */
+  double *const *dst;                            /* [2][nto]: neighbour k's ghost-vector window for me, per parity   */
+  unsigned long long *const *rflag;              /* [nto]  arrival flag on neighbour k (its flag[my rank])           */
+  const unsigned long long *const *lcredit;      /* [nto]  local credit written by neighbour k (consumed exchange)   */
+  unsigned long long *const *rcredit;            /* [nfrom] credit slot on sender k (its credit[my rank])            */
+  const unsigned long long *const *lflag;        /* [nfrom] local arrival flag written by sender k                   */
+};
+
 /* Every wait on a peer is bounded: a rank that died (or a collective called out of order) must end in a loud failure
  * (the kernel traps, the next CUDA call reports it), never in a GPU that spins for ever.  ~60 s of SM cycles. */
 #define B200_SPIN_LIMIT_CYCLES (120ll * 1000ll * 1000ll * 1000ll)

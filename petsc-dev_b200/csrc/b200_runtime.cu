@@ -93,6 +93,8 @@ extern "C" int b200_finalize(void)
 extern "C" int b200_set_stream(void *s)
 {
   B200_NEED_INIT();
+  if (s) g_b200.multi_stream = true;
+  else if (g_b200.multi_stream) { B200_CUDA(cudaDeviceSynchronize()); g_b200.multi_stream = false; }   /* back on one stream: nothing in flight elsewhere */
   g_b200.stream = s ? (cudaStream_t)s : g_b200.own_stream;
   return 0;
 }

@@ -500,6 +500,15 @@ int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *
 int b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out)
 {
   const B200Seq *Sa = &A->A, *Sb = &A->B;
+  if (A->fusedplan) {
+    B200_CHK(b200_mpiaij_mult_fused(A, x, NULL, y, false, true));
+    if (!dot_out) return 0;
+    const double *p; int n;
+    b200_mpiaij_fused_dotparts(A, &p, &n);
+    dot_final_kernel<<<1, 1024, 0, g_b200.stream>>>(n, p, 0, NULL, dot_out);
+    B200_LAUNCHED(1);
+    return 0;
+  }
   if (Sa->compressed || Sa->m != Sa->n || Sa->nstrips > 1 || Sb->nstrips > 1) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square, uncompressed, unstripped diagonal block");
   B200_CHK(b200_mpiaij_exchange_begin(A, x));
   B200_CHK(b200_seq_mult_ex(Sa, x, NULL, y, false, true, x, NULL));
@@ -624,11 +633,9 @@ extern "C" int b200_mat_mult(b200_mat A, const double *x, double *y)
   if (!A || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   if (x == y) return b200_seterr(B200_ERR_ARG_IDN, "x and y must be different vectors");   /* matrix.c:2143 */
   if (A->kind == 0) return b200_seq_mult(&A->A, x, NULL, y, false, NULL);
-  /* MatMult_MPIAIJ mpiaij.c:1102-1116: scatter begin | diagonal block | scatter end | off-diagonal multadd */
-  B200_CHK(b200_mpiaij_exchange_begin(A, x));
-  B200_CHK(b200_seq_mult(&A->A, x, NULL, y, false, NULL));
-  B200_CHK(b200_mpiaij_exchange_end(A));
-  return b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], y, y, true, NULL);
+  /* MatMult_MPIAIJ mpiaij.c:1102-1116: scatter begin | diagonal block | scatter end | off-diagonal multadd —
+   * one kernel when the operator has a one-launch plan, else the four steps (b200_comm.cu) */
+  return b200_mpiaij_mult(A, x, NULL, y, false);
 }
 
 /* diagnostic: one MPIAIJ MatMult with CUDA events between its phases (exchange begin | diagonal block | exchange end |
@@ -663,10 +670,7 @@ extern "C" int b200_mat_multadd(b200_mat A, const double *x, const double *y, do
   if (x == z) return b200_seterr(B200_ERR_ARG_IDN, "x and z must be different vectors");
   if (A->kind == 0) return b200_seq_mult(&A->A, x, y, z, true, NULL);
   /* MatMultAdd_MPIAIJ mpiaij.c:1132-1143 */
-  B200_CHK(b200_mpiaij_exchange_begin(A, x));
-  B200_CHK(b200_seq_mult(&A->A, x, y, z, true, NULL));
-  B200_CHK(b200_mpiaij_exchange_end(A));
-  return b200_seq_mult(&A->B, A->d_lvec[A->epoch & 1], z, z, true, NULL);
+  return b200_mpiaij_mult(A, x, y, z, true);
 }
 
 extern "C" int b200_mat_multtranspose(b200_mat A, const double *x, double *y)
@@ -744,6 +748,8 @@ extern "C" int b200_mat_destroy(b200_mat A)
   if (A->batchplan) b200_batchplan_free(A->batchplan);
   if (A->kind) {
     b200_seq_free(&A->B);
+    b200_mpiaij_fused_free(A);
+    if (A->ev_done) cudaEventDestroy(A->ev_done);
     if (A->peerplan) b200_mpiaij_peer_free(A);
     cudaFree(A->d_ghost_t);
     cudaFree(A->d_garray); cudaFree(A->d_lvec[0]); cudaFree(A->d_lvec[1]); cudaFree(A->d_to_indices); cudaFree(A->d_sendbuf);

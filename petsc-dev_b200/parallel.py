@@ -181,6 +181,30 @@ def enable_p2p(rank=None, size=None, dist=None, strict=True):
     return True
 
 
+def enable_loopback():
+    """Peer-memory transport on a ONE-rank communicator: the rank is its own neighbour (b200_comm_enable_p2p(2)).  The
+    exchange kernels, arrival flags and credits run as between GPUs; used by the single-GPU tests of the multi-GPU path."""
+    _chk(lib.b200_comm_enable_p2p(2), "b200_comm_enable_p2p (loop-back)")
+
+
+def create_mpiaij_raw(m, N, Ai, Aj, Aa, Bi, Bj, Ba, garray, to_procs, to_starts, to_indices, from_procs, from_starts):
+    """b200_mat_create_mpiaij from explicit pieces (tests)."""
+    Ai, Aj, Aa, Bi, Bj, Ba = _i32(Ai), _i32(Aj), _f64(Aa), _i32(Bi), _i32(Bj), _f64(Ba)
+    g, tp, ts, ti, fp, fs = _i32(garray), _i32(to_procs), _i32(to_starts), _i32(to_indices), _i32(from_procs), _i32(from_starts)
+    h = C.c_void_p()
+    _chk(lib.b200_mat_create_mpiaij(int(m), int(m), int(N), _ip(Ai), _ip(Aj), _dp(Aa), int(g.size), _ip(Bi), _ip(Bj), _dp(Ba), _ip(g),
+                                    int(tp.size), _ip(tp), _ip(ts), _ip(ti), int(fp.size), _ip(fp), _ip(fs), C.byref(h)),
+         "MatAssemblyEnd_MPIAIJ (upload)")
+    return Mat(h, m, m)
+
+
+def is_fused(A):
+    """(one-launch MatMult?, number of boundary tiles)"""
+    f, nb = C.c_int(), C.c_int()
+    _chk(lib.b200_mat_mpiaij_is_fused(A.h, C.byref(f), C.byref(nb)), "b200_mat_mpiaij_is_fused")
+    return bool(f.value), nb.value
+
+
 def p2p_enabled():
     e = C.c_int()
     _chk(lib.b200_comm_p2p_enabled(C.byref(e)), "b200_comm_p2p_enabled")

@@ -221,3 +221,27 @@ def elements_hex3d(nx, seed=11, scale_values=True):
 def random_vector_at(idx, seed, lo=-1.0, hi=1.0):
     """Entries idx (global ids) of the vector random_vector(N, seed) — what a rank's ghost vector holds."""
     return lo + (hi - lo) * u01(hash3(seed, np.asarray(idx, dtype=np.uint64), 0))
+
+
+def periodic_z_loopback(nx, ny, nz):
+    """The 7-point Laplacian, periodic in z, written the way ONE rank of a parallel matrix would hold it if its only
+    neighbour were itself: A_d = the non-periodic stencil (local columns), B = the wrap-around couplings (-1) with ghost
+    ids, to_idx = the local entry every ghost is a copy of (ghosts [0, nx*ny) mirror the top plane, the rest the bottom
+    plane).  Returns dict(m, Ad=(i,j,a), B=(i,j,a), nghost, to_idx, full=(i,j,a) — the same operator as one SeqAIJ matrix)."""
+    import scipy.sparse as sp
+    m, npl = nx * ny * nz, nx * ny
+    ai, aj, aa = laplace3d_7pt(nx, ny, nz)
+    rows_bot, rows_top = np.arange(npl), np.arange(m - npl, m)
+    bcnt = np.zeros(m, np.int64)
+    bcnt[rows_bot] = 1
+    bcnt[rows_top] += 1                                   # nz == 1 would double up: not used
+    bi = np.concatenate([[0], np.cumsum(bcnt)])
+    bj = np.concatenate([np.arange(npl), np.arange(npl, 2 * npl)]).astype(np.int32)     # bottom rows read ghosts 0.., top rows the rest
+    ba = -np.ones(2 * npl)
+    to_idx = np.concatenate([rows_top, rows_bot]).astype(np.int32)
+    A = sp.csr_matrix((aa, aj, ai), shape=(m, m))
+    W = sp.csr_matrix((ba, to_idx[bj], bi), shape=(m, m))
+    F = (A + W).tocsr()
+    F.sort_indices()
+    return dict(m=m, Ad=(ai, aj, aa), B=(bi, bj, ba), nghost=2 * npl, to_idx=to_idx,
+                full=(F.indptr.astype(np.int64), F.indices.astype(np.int32), F.data.astype(np.float64)))
