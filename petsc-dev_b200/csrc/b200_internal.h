@@ -136,6 +136,10 @@ void b200_mpiaij_peer_free(b200_mat A);
 void b200_batchplan_free(void *plan);
 bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox);
 
+struct CgState;
+bool b200_cg_persistent_ok(b200_mat A);
+int  b200_cg_persistent_run(b200_mat A, int jacobi, const double *d, double *X, double *R, double *ZW, double *P, CgState *ds, double *dhist, int iters);
+
 /* reduction grid helper */
 static inline int b200_red_grid(long long n, int threads, int per_thread)
 {

@@ -19,10 +19,10 @@
  */
 #include "b200_internal.h"
 #include "b200_p2p_dev.cuh"
+#include "b200_ksp_state.h"
 #include <math.h>
 #include <vector>
 
-#define KSP_ERR_FP_REASON (-100)   /* internal: NaN/Inf in a CG dot product -> PETSC_ERR_FP (cg.c:152,213,278) */
 
 /* ------------------------------------------------------------------------------------------------ operator */
 static int op_mult(b200_mat A, const double *x, double *y) { return b200_mat_mult(A, x, y); }
@@ -173,24 +173,6 @@ static int cg_reference_sequence(b200_mat A, const Pc *pc, Conv *cv, int max_it,
 }
 
 /* ------------------------------------------------------------------------------------------------ CG, fused */
-struct CgState {
-  double beta, betaold, dpi, dpiold, a, b, dp, ttol, rnorm0, abstol, dtol;
-  double red[4];            /* [0] z.z  [1] z.r  [2] r.r  [3] p.w   (local, then all-reduced in place) */
-  int    i, its, reason, max_it, normtype, nhist, histmax, pad;
-};
-
-__device__ __forceinline__ bool bad(double v) { return isnan(v) || isinf(v); }
-
-/* top of loop iteration i (cg.c:181-199): decides whether the iteration runs and fixes b */
-__device__ void cg_top(CgState *s)
-{
-  s->its = s->i + 1;
-  if (s->beta == 0.0) { s->reason = B200_KSP_CONVERGED_ATOL; return; }
-  if (s->i > 0 && s->beta * s->betaold < 0.0) { s->reason = B200_KSP_DIVERGED_INDEFINITE_PC; return; }
-  s->b = (s->i == 0) ? 0.0 : s->beta / s->betaold;
-  s->dpiold = s->dpi;
-}
-
 __global__ void cg_begin_kernel(CgState *s) { if (threadIdx.x == 0 && s->reason == 0) cg_top(s); }
 
 /* after p.w is known (cg.c:207-220) */
@@ -239,35 +221,6 @@ __global__ void __launch_bounds__(256) cg_parts_kernel(CgState *s, const CgParts
   if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = t;
   __syncthreads();
   if (threadIdx.x == 0) { double u = 0.0; for (int q = 0; q < 8; q++) u += s_w[q]; s->red[3] = u; }
-}
-
-/* after the update kernel's reductions (cg.c:227-281): norm, history, KSPDefaultConverged, new beta, next top */
-__device__ void cg_after_update_body(CgState *s, double *hist)   /* one thread; s->reason == 0 on entry */
-{
-  double dp, beta = s->beta;
-  if (s->normtype == B200_KSP_NORM_PRECONDITIONED) dp = sqrt(s->red[0]);
-  else if (s->normtype == B200_KSP_NORM_UNPRECONDITIONED) dp = sqrt(s->red[2]);
-  else if (s->normtype == B200_KSP_NORM_NATURAL) {
-    beta = s->red[1];
-    if (bad(beta)) { s->reason = KSP_ERR_FP_REASON; return; }
-    dp = sqrt(fabs(beta));
-  } else dp = 0.0;
-  s->dp = dp;
-  if (hist && s->histmax > s->nhist) hist[s->nhist++] = dp;
-  if (s->normtype != B200_KSP_NORM_NONE) {
-    if (bad(dp)) s->reason = B200_KSP_DIVERGED_NAN;
-    else if (dp <= s->ttol) s->reason = (dp < s->abstol) ? B200_KSP_CONVERGED_ATOL : B200_KSP_CONVERGED_RTOL;
-    else if (dp >= s->dtol * s->rnorm0) s->reason = B200_KSP_DIVERGED_DTOL;
-    if (s->reason) return;
-  }
-  if (s->normtype != B200_KSP_NORM_NATURAL) {
-    beta = s->red[1];
-    if (bad(beta)) { s->reason = KSP_ERR_FP_REASON; return; }
-  }
-  s->beta = beta;
-  s->i++;
-  if (s->i >= s->max_it) { s->reason = B200_KSP_DIVERGED_ITS; return; }
-  cg_top(s);
 }
 
 __global__ void __launch_bounds__(64) cg_after_update_kernel(CgState *s, double *hist, const CgAr ar)
@@ -490,10 +443,17 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
   int gp = ((n + 1) / 2 + 255) / 256; if (gp > B200_NSM * 16) gp = B200_NSM * 16; if (gp < 1) gp = 1;
   const int gu = b200_red_grid((n + 1) / 2, 512, 2);
   if (check_every < 1) check_every = 1;
+  /* short iterations: the whole block of iterations as ONE persistent cooperative kernel (b200_ksp_persist.cu); it leaves
+   * early when the device-side convergence test fires, so the host need not look often */
+  const bool persist = !multi && seq && b200_cg_persistent_ok(A);
+  if (persist && check_every < 256) check_every = 256;
   int launched = 0, rc = 0;
   while (launched < max_it) {
     int batch = check_every;
     if (launched + batch > max_it) batch = max_it - launched;
+    if (persist) {
+      rc = b200_cg_persistent_run(A, pc->type == 1, pc->d, X, R, Z, P, ds, dhist, batch); if (rc) goto done;
+    } else
     for (int k = 0; k < batch; k++) {
       cg_pupdate_kernel<<<gp, 256, 0, st>>>(n, ds, P, Z);
       B200_LAUNCHED(1);
