@@ -545,13 +545,14 @@ struct FusedPlan {
   int4  *d_tiles;
   int   *d_flag;
   double *d_dotpart;
+  unsigned *d_ticket_dot;
 };
 
 void b200_mpiaij_fused_free(b200_mat M)
 {
   FusedPlan *fp = (FusedPlan *)M->fusedplan;
   if (!fp) return;
-  cudaFree(fp->d_tiles); cudaFree(fp->d_flag); cudaFree(fp->d_dotpart);
+  cudaFree(fp->d_tiles); cudaFree(fp->d_flag); cudaFree(fp->d_dotpart); cudaFree(fp->d_ticket_dot);
   free(fp);
   M->fusedplan = NULL;
 }
@@ -565,22 +566,20 @@ void b200_mpiaij_fused_dotparts(b200_mat A, const double **p, int *n)
 }
 
 typedef void (*fused_kern_t)(const MpiSpmvArgs);
-template <int G, int MINB> static fused_kern_t fused_pick(bool add, bool dot)
+template <int G> static fused_kern_t fused_pick(bool add, bool dot)
 {
-  if (add) return dot ? spmv_mpiaij_kernel<G, true, true, 256, 2048, MINB> : spmv_mpiaij_kernel<G, true, false, 256, 2048, MINB>;
-  return dot ? spmv_mpiaij_kernel<G, false, true, 256, 2048, MINB> : spmv_mpiaij_kernel<G, false, false, 256, 2048, MINB>;
+  if (add) return dot ? spmv_mpiaij_kernel<G, true, true, 256, 2048> : spmv_mpiaij_kernel<G, true, false, 256, 2048>;
+  return dot ? spmv_mpiaij_kernel<G, false, true, 256, 2048> : spmv_mpiaij_kernel<G, false, false, 256, 2048>;
 }
-static int g_fused_minb = -1;
 static fused_kern_t fused_kernel(int G, bool add, bool dot)
 {
-  if (g_fused_minb < 0) { const char *e = getenv("B200_MPI_FUSED_OCC8"); g_fused_minb = (e && !atoi(e)) ? 1 : 8; }
   switch (G) {
-    case 1:  return g_fused_minb == 8 ? fused_pick<1, 8>(add, dot) : fused_pick<1, 1>(add, dot);
-    case 2:  return fused_pick<2, 1>(add, dot);
-    case 4:  return fused_pick<4, 1>(add, dot);
-    case 8:  return fused_pick<8, 1>(add, dot);
-    case 16: return fused_pick<16, 1>(add, dot);
-    default: return fused_pick<32, 1>(add, dot);
+    case 1:  return fused_pick<1>(add, dot);
+    case 2:  return fused_pick<2>(add, dot);
+    case 4:  return fused_pick<4>(add, dot);
+    case 8:  return fused_pick<8>(add, dot);
+    case 16: return fused_pick<16>(add, dot);
+    default: return fused_pick<32>(add, dot);
   }
 }
 
@@ -627,6 +626,8 @@ static int fusedplan_build(b200_mat M, const int *Bi)
   B200_CUDA(cudaMalloc((void **)&fp->d_flag, sizeof(int) * flag.size()));
   B200_CUDA(cudaMemcpy(fp->d_flag, flag.data(), sizeof(int) * flag.size(), cudaMemcpyHostToDevice));
   B200_CUDA(cudaMalloc((void **)&fp->d_dotpart, sizeof(double) * (size_t)(fp->grid + 1)));
+  B200_CUDA(cudaMalloc((void **)&fp->d_ticket_dot, sizeof(unsigned)));
+  B200_CUDA(cudaMemset(fp->d_ticket_dot, 0, sizeof(unsigned)));
   M->fusedplan = fp;
   return 0;
 }
@@ -641,7 +642,11 @@ extern "C" int b200_mat_mpiaij_is_fused(b200_mat A, int *fused, int *boundary_ti
 
 /* z = (add ? yin : 0) + A_d x + B ghost(x), exchange included, in ONE launch.  want_dot: per-CTA partials of x . (z - yin)
  * are left for the caller (b200_mpiaij_fused_dotparts). */
-int b200_mpiaij_mult_fused(b200_mat M, const double *x, const double *yin, double *z, bool add, bool want_dot)
+int b200_mpiaij_mult_fused(b200_mat M, const double *x, const double *yin, double *z, bool add, bool want_dot) { return b200_mpiaij_mult_fused_cg(M, x, yin, z, add, want_dot, NULL, NULL); }
+
+/* cg != NULL (with want_dot): the kernel's last CTA also finishes x . z -> cg->red[3], all-reduces it (ar) and runs the CG
+ * scalar step that follows p.w */
+int b200_mpiaij_mult_fused_cg(b200_mat M, const double *x, const double *yin, double *z, bool add, bool want_dot, CgState *cg, const CgAr *ar)
 {
   B200Ctx &c = g_b200;
   FusedPlan *fp = (FusedPlan *)M->fusedplan;
@@ -662,6 +667,8 @@ int b200_mpiaij_mult_fused(b200_mat M, const double *x, const double *yin, doubl
   a.to_idx = M->d_to_indices;
   a.plan = pp->dev;
   a.parity = (int)(M->epoch & 1); a.epoch = (unsigned long long)M->epoch; a.ticket = pp->d_ticket;
+  a.cg = want_dot ? cg : NULL; a.ticket_dot = fp->d_ticket_dot;
+  if (a.cg && ar) a.ar = *ar; else a.ar.size = 1;
   fused_kernel(M->A.G, add, want_dot)<<<fp->grid, fp->threads, SpmvSmem<256, 2048, 1>::BYTES, c.stream>>>(a);
   B200_LAUNCHED(1);
   return 0;

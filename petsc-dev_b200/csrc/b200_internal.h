@@ -123,6 +123,8 @@ int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_ou
 int  b200_mpiaij_mult(b200_mat A, const double *x, const double *yin, double *z, bool add);   /* MatMult / MatMultAdd of the parallel type */
 bool b200_mpiaij_fused(b200_mat A);
 int  b200_mpiaij_mult_fused(b200_mat A, const double *x, const double *yin, double *z, bool add, bool want_dot);
+struct CgState; struct CgAr;
+int  b200_mpiaij_mult_fused_cg(b200_mat A, const double *x, const double *yin, double *z, bool add, bool want_dot, CgState *cg, const CgAr *ar);
 void b200_mpiaij_fused_dotparts(b200_mat A, const double **p, int *n);
 void b200_mpiaij_fused_free(b200_mat A);
 

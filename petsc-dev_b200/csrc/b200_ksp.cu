@@ -176,8 +176,6 @@ static int cg_reference_sequence(b200_mat A, const Pc *pc, Conv *cv, int max_it,
 __global__ void cg_begin_kernel(CgState *s) { if (threadIdx.x == 0 && s->reason == 0) cg_top(s); }
 
 /* after p.w is known (cg.c:207-220) */
-struct CgAr { unsigned long long seq; unsigned long long *const *inbox; int rank, size; };   /* size <= 1: no allreduce */
-
 struct CgParts { const double *a; int na; const double *b; int nb; };   /* per-CTA partials of p.w left by the SpMV kernels */
 
 __global__ void __launch_bounds__(256) cg_after_dot_kernel(CgState *s, const CgAr ar, const CgParts parts)
@@ -203,11 +201,7 @@ __global__ void __launch_bounds__(256) cg_after_dot_kernel(CgState *s, const CgA
   if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[3], 1, 0, ar.seq, ar.rank, ar.size, ar.inbox);
   else __syncthreads();
   if (threadIdx.x != 0 || s->reason != 0) return;
-  s->dpi = s->red[3];
-  s->betaold = s->beta;
-  if (bad(s->dpi)) { s->reason = KSP_ERR_FP_REASON; return; }
-  if (s->dpi == 0.0 || (s->i > 0 && s->dpi * s->dpiold <= 0.0)) { s->reason = B200_KSP_DIVERGED_INDEFINITE_MAT; return; }
-  s->a = s->beta / s->dpi;
+  cg_after_dot_body(s);
 }
 
 __global__ void __launch_bounds__(256) cg_parts_kernel(CgState *s, const CgParts parts)   /* NCCL transport: local p.w only */
@@ -264,13 +258,18 @@ __global__ void __launch_bounds__(256) cg_pupdate_kernel(int n, const CgState *_
 template <bool JACOBI, bool INLINE_AFTER>
 __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, double *__restrict__ x, const double *__restrict__ p,
                                                         double *__restrict__ r, const double *__restrict__ w, double *__restrict__ z,
-                                                        const double *__restrict__ d, double *partials, unsigned *ticket, double *hist)
+                                                        const double *__restrict__ d, double *partials, unsigned *ticket, double *hist,
+                                                        const CgAr ar)
 {
-  if (s->reason != 0) return;
+  /* ar.size > 1 (INLINE_AFTER only): the three sums are all-reduced over peer memory by the last CTA, which then runs the
+   * scalar step.  That allreduce is collective, so a finished solve (reason != 0, the same on every rank) still goes
+   * through it with zero sums; without it the kernel just returns. */
+  const bool active = (s->reason == 0);
+  if (!active && ar.size <= 1) return;
   const double a = s->a, ma = -a;
   double zz = 0.0, zr = 0.0, rr = 0.0;
   const int stride = gridDim.x * blockDim.x;
-  const int n2 = n >> 1;
+  const int n2 = active ? (n >> 1) : 0;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n2; i += stride) {
     double2 xv = reinterpret_cast<double2 *>(x)[i];
     const double2 pv = reinterpret_cast<const double2 *>(p)[i];
@@ -288,7 +287,7 @@ __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, doubl
     zr += zv.x * rv.x; zr += zv.y * rv.y;
     rr += rv.x * rv.x; rr += rv.y * rv.y;
   }
-  if ((n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
+  if (active && (n & 1) && blockIdx.x == 0 && threadIdx.x == 0) {
     const int i = n - 1;
     const double xv = x[i] + a * p[i], rv = r[i] + ma * w[i], zv = JACOBI ? rv * d[i] : rv;
     x[i] = xv; r[i] = rv; z[i] = zv;
@@ -337,11 +336,12 @@ __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, doubl
       if (lane == 0) s->red[q] = u;
     }
   }
-  if (threadIdx.x == 0) {
-    *ticket = 0;
-    /* single rank: the scalar recurrences that follow (norm, convergence test, new beta) need no allreduce and run here,
-     * in the last CTA, instead of in a kernel of their own (thread 0 wrote red[] itself) */
-    if (INLINE_AFTER) cg_after_update_body(s, hist);
+  if (threadIdx.x == 0) *ticket = 0;
+  if (INLINE_AFTER) {
+    /* the scalar recurrences that follow (norm, convergence test, new beta) run here, in the last CTA, instead of in a
+     * kernel of their own (thread 0 wrote red[] itself) */
+    if (ar.size > 1) b200_p2p_allreduce_cta(&s->red[0], 3, 0, ar.seq, ar.rank, ar.size, ar.inbox);
+    if (threadIdx.x == 0 && active) cg_after_update_body(s, hist);
   }
 }
 
@@ -459,9 +459,21 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
       B200_LAUNCHED(1);
       CgAr ar1 = {0, NULL, c.rank, 1}, ar2 = {0, NULL, c.rank, 1};
       CgParts parts = {NULL, 0, NULL, 0};
+      bool dot_done = false;                      /* p.w, its allreduce and the scalar step after it already ran */
       if (seq) {
         rc = b200_seq_mult_ex(&A->A, P, NULL, W, false, true, P, NULL); if (rc) goto done;
         b200_seq_dotparts(&A->A, &parts.a, &parts.na);
+      } else if (mpi_dot && b200_mpiaij_fused(A)) {
+        /* one launch: ghost exchange + both blocks + p.w; over peer memory its last CTA also all-reduces p.w and takes the
+         * scalar step */
+        if (!multi || b200_p2p_next(&ar1.seq, &ar1.inbox)) {
+          if (multi) ar1.size = c.size;
+          rc = b200_mpiaij_mult_fused_cg(A, P, NULL, W, false, true, ds, &ar1); if (rc) goto done;
+          dot_done = true;
+        } else {
+          rc = b200_mpiaij_mult_fused(A, P, NULL, W, false, true); if (rc) goto done;
+          b200_mpiaij_fused_dotparts(A, &parts.a, &parts.na);
+        }
       } else if (mpi_dot) {
         rc = b200_mpiaij_mult_dot(A, P, W, NULL); if (rc) goto done;
         b200_seq_dotparts(&A->A, &parts.a, &parts.na);
@@ -472,29 +484,33 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
         B200_LAUNCHED(1);
       }
       /* p.w: final reduction of the SpMV partials + allreduce (peer memory) + the scalar step, one kernel */
-      if (multi) {
-        if (b200_p2p_next(&ar1.seq, &ar1.inbox)) ar1.size = c.size;
-        else {
-          if (parts.na + parts.nb > 0) {          /* NCCL needs the local sum in memory first */
-            cg_parts_kernel<<<1, 256, 0, st>>>(ds, parts); B200_LAUNCHED(1);
-            parts.na = parts.nb = 0;
+      if (!dot_done) {
+        if (multi) {
+          if (b200_p2p_next(&ar1.seq, &ar1.inbox)) ar1.size = c.size;
+          else {
+            if (parts.na + parts.nb > 0) {          /* NCCL needs the local sum in memory first */
+              cg_parts_kernel<<<1, 256, 0, st>>>(ds, parts); B200_LAUNCHED(1);
+              parts.na = parts.nb = 0;
+            }
+            rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done;
           }
-          rc = b200_comm_allreduce_dev(&ds->red[3], 1, 0); if (rc) goto done;
         }
-      }
-      cg_after_dot_kernel<<<1, 256, 0, st>>>(ds, ar1, parts);
-      B200_LAUNCHED(1);
-      if (multi) {
-        if (pc->type == 1) cg_update_kernel<true, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist);
-        else               cg_update_kernel<false, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist);
+        cg_after_dot_kernel<<<1, 256, 0, st>>>(ds, ar1, parts);
         B200_LAUNCHED(1);
-        if (b200_p2p_next(&ar2.seq, &ar2.inbox)) ar2.size = c.size;
-        else { rc = b200_comm_allreduce_dev(&ds->red[0], 3, 0); if (rc) goto done; }
+      }
+      if (multi && !b200_p2p_next(&ar2.seq, &ar2.inbox)) {
+        /* NCCL transport: update, allreduce, scalar step as three launches */
+        if (pc->type == 1) cg_update_kernel<true, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist, ar2);
+        else               cg_update_kernel<false, false><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist, ar2);
+        B200_LAUNCHED(1);
+        rc = b200_comm_allreduce_dev(&ds->red[0], 3, 0); if (rc) goto done;
         cg_after_update_kernel<<<1, 64, 0, st>>>(ds, dhist, ar2);
         B200_LAUNCHED(1);
       } else {
-        if (pc->type == 1) cg_update_kernel<true, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist);
-        else               cg_update_kernel<false, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist);
+        /* the last CTA all-reduces z.z, z.r, r.r over peer memory (one rank: nothing to reduce) and takes the scalar step */
+        if (multi) ar2.size = c.size;
+        if (pc->type == 1) cg_update_kernel<true, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, pc->d, c.d_partials, c.d_ticket, dhist, ar2);
+        else               cg_update_kernel<false, true><<<gu, 512, 0, st>>>(n, ds, X, P, R, W, Z, NULL, c.d_partials, c.d_ticket, dhist, ar2);
         B200_LAUNCHED(1);
       }
     }

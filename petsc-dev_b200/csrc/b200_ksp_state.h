@@ -13,7 +13,20 @@ struct CgState {
   int    i, its, reason, max_it, normtype, nhist, histmax, pad;
 };
 
+/* an allreduce over peer memory issued from inside a kernel (b200_p2p_allreduce_cta); size <= 1: none */
+struct CgAr { unsigned long long seq; unsigned long long *const *inbox; int rank, size; };
+
 static __device__ __forceinline__ bool bad(double v) { return isnan(v) || isinf(v); }
+
+/* after p.w is known, red[3] (cg.c:207-220): one thread; s->reason == 0 on entry */
+static __device__ __forceinline__ void cg_after_dot_body(CgState *s)
+{
+  s->dpi = s->red[3];
+  s->betaold = s->beta;
+  if (bad(s->dpi)) { s->reason = KSP_ERR_FP_REASON; return; }
+  if (s->dpi == 0.0 || (s->i > 0 && s->dpi * s->dpiold <= 0.0)) { s->reason = B200_KSP_DIVERGED_INDEFINITE_MAT; return; }
+  s->a = s->beta / s->dpi;
+}
 
 /* top of loop iteration i (cg.c:181-199): decides whether the iteration runs and fixes b */
 static __device__ __forceinline__ void cg_top(CgState *s)

@@ -20,6 +20,7 @@
 #define B200_SPMV_MPI_KERNELS_CUH
 #include "b200_spmv_kernels.cuh"
 #include "b200_p2p_dev.cuh"
+#include "b200_ksp_state.h"
 
 struct MpiSpmvArgs {
   int           ntiles;
@@ -37,6 +38,11 @@ struct MpiSpmvArgs {
   int           parity;
   unsigned long long epoch;
   unsigned     *ticket;
+  /* CG (DOT only, cg != NULL): the last CTA to finish sums the partials of p.w in a fixed order, all-reduces the sum over
+   * peer memory and runs the scalar step that follows it (cg.c:207-220) — no kernel of its own for that */
+  CgState      *cg;
+  CgAr          ar;
+  unsigned     *ticket_dot;
 };
 
 /* The off-diagonal entries of one row, lane g of G striding them, added to `sum` in order (kept out of line: it runs for
@@ -50,10 +56,11 @@ __device__ __noinline__ double b200_offdiag_row(const int *__restrict__ bi, cons
   return sum;
 }
 
-/* MINB: resident CTAs per SM the register allocation is held to (8 = the sequential kernel's occupancy, at the price of a
- * few spilled words in the tile loop; 1 = whatever the kernel needs, 6 CTAs per SM) — chosen at run time, b200_comm.cu */
-template <int G, bool ADD, bool DOT, int THREADS, int TILE_NNZ, int MINB>
-__global__ void __launch_bounds__(THREADS, MINB)
+/* 6 resident CTAs per SM = the 40 registers the kernel wants.  Holding it to the sequential kernel's 8 CTAs (32 registers)
+ * spills ~50 bytes inside the tile loop and was measured 1.7x SLOWER on 2 GPUs (0.441 ms against 0.258 ms per 256^3
+ * product, profiles/r02_bench_n2_*.json), so that variant is gone. */
+template <int G, bool ADD, bool DOT, int THREADS, int TILE_NNZ>
+__global__ void __launch_bounds__(THREADS, 6)
 spmv_mpiaij_kernel(const MpiSpmvArgs a)
 {
   constexpr int SE = TILE_NNZ + SPMV_ALIGN_PAD;
@@ -205,6 +212,30 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0) a.dotpart[blockIdx.x] = v;
+    }
+    if (a.cg) {
+      if (tid == 0) { __threadfence(); s_last = (atomicAdd(a.ticket_dot, 1u) == gridDim.x - 1u); }
+      __syncthreads();
+      if (s_last) {                                   /* CTA-uniform */
+        __threadfence();
+        double u = 0.0;
+        for (int i = tid; i < (int)gridDim.x; i += THREADS) u += __ldcg(&a.dotpart[i]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+        if (lane == 0) s_red[wid] = u;
+        __syncthreads();
+        if (tid == 0) {
+          double v = 0.0;
+#pragma unroll
+          for (int q = 0; q < THREADS / 32; q++) v += s_red[q];
+          a.cg->red[3] = v;
+          *a.ticket_dot = 0;
+        }
+        /* collective: every rank runs it whatever cg->reason says */
+        if (a.ar.size > 1) b200_p2p_allreduce_cta(&a.cg->red[3], 1, 0, a.ar.seq, a.ar.rank, a.ar.size, a.ar.inbox);
+        else __syncthreads();
+        if (tid == 0 && a.cg->reason == 0) cg_after_dot_body(a.cg);
+      }
     }
   }
 }

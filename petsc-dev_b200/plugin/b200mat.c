@@ -23,11 +23,14 @@ extern PetscInt PetscB200MatUploads, PetscB200MatValueUpdates;
 
 #define CHKB200(call) do { int b200rc_ = (call); if (b200rc_) SETERRQ2(PETSC_COMM_SELF,PETSC_ERR_LIB,"libpetscb200 error %d: %s",b200rc_,b200_last_error()); } while (0)
 
+typedef unsigned long long B200Hash;
+
 typedef struct {
   b200_mat  mat;          /* device CSR + row binning                           */
   PetscInt  state;        /* object state of the host matrix at the last upload */
   PetscInt  m,nz;
   PetscInt *i;            /* host copy of the uploaded row offsets              */
+  B200Hash  jhash;        /* hash of the uploaded column indices                */
 } Mat_SeqAIJB200;
 
 typedef struct {
@@ -35,7 +38,26 @@ typedef struct {
   PetscInt  state,stateA,stateB;
   PetscInt  m,nzA,nzB,nghost;
   PetscInt *iA,*iB,*garray; /* host copies of what was uploaded: row offsets of both blocks, ghost columns */
+  B200Hash  jhashA,jhashB;  /* hashes of the uploaded column indices of both blocks                          */
 } Mat_MPIAIJB200;
+
+/* Hash of a column-index array.  Equal row offsets do not imply equal columns: MatZeroRows with a diagonal value on a row
+ * whose single entry was off the diagonal rewrites a->j in place (aij.c:1680-1683) and leaves i and nz alone.  Four
+ * independent multiply-xor lanes keep it at memory speed (the check reads 4 bytes per nonzero; the value refresh it
+ * guards moves 8 over PCIe). */
+static B200Hash MatB200HashInts(const PetscInt *v,PetscInt n)
+{
+  const B200Hash K = 0x9E3779B97F4A7C15ull;
+  B200Hash       h0 = 1,h1 = 2,h2 = 3,h3 = 4;
+  PetscInt       k = 0;
+  for (; k+4<=n; k+=4) {
+    h0 = (h0 ^ (B200Hash)(unsigned)v[k])*K;   h1 = (h1 ^ (B200Hash)(unsigned)v[k+1])*K;
+    h2 = (h2 ^ (B200Hash)(unsigned)v[k+2])*K; h3 = (h3 ^ (B200Hash)(unsigned)v[k+3])*K;
+  }
+  for (; k<n; k++) h0 = (h0 ^ (B200Hash)(unsigned)v[k])*K;
+  h0 ^= h0>>29; h1 ^= h1>>31; h2 ^= h2>>33; h3 ^= h3>>27;
+  return ((h0*K ^ h1)*K ^ h2)*K ^ h3;
+}
 
 /* ------------------------------------------------------------------------------------------------ sequential */
 #undef __FUNCT__
@@ -53,6 +75,7 @@ static PetscErrorCode MatB200CopyToDevice_SeqAIJ(Mat A)                         
   if (d->mat && d->state == ((PetscObject)A)->state) PetscFunctionReturn(0);
   if (d->mat && d->m == m && d->nz == a->nz) {
     ierr = PetscMemcmp(d->i,a->i,(m+1)*sizeof(PetscInt),&same);CHKERRQ(ierr);
+    if (same && MatB200HashInts(a->j,a->nz) != d->jhash) same = PETSC_FALSE;
   }
   if (same) {
     CHKB200(b200_mat_update_values(d->mat,a->a));
@@ -64,7 +87,7 @@ static PetscErrorCode MatB200CopyToDevice_SeqAIJ(Mat A)                         
     CHKB200(b200_mat_create_seqaij(m,A->cmap->n,a->i,a->j,a->a,&d->mat));
     ierr = PetscMalloc((m+1)*sizeof(PetscInt),&d->i);CHKERRQ(ierr);
     ierr = PetscMemcpy(d->i,a->i,(m+1)*sizeof(PetscInt));CHKERRQ(ierr);
-    d->m = m; d->nz = a->nz;
+    d->m = m; d->nz = a->nz; d->jhash = MatB200HashInts(a->j,a->nz);
     PetscB200MatUploads++;
     ierr = PetscInfo1(A,"B200 device copy: full upload (%D nonzeros)\n",a->nz);CHKERRQ(ierr);
   }
@@ -333,6 +356,7 @@ static PetscErrorCode MatB200CopyToDevice_MPIAIJ(Mat A)
     ierr = PetscMemcmp(d->iB,ao->i,(d->m+1)*sizeof(PetscInt),&sB);CHKERRQ(ierr);
     if (nghost) { ierr = PetscMemcmp(d->garray,a->garray,nghost*sizeof(PetscInt),&sG);CHKERRQ(ierr); }
     same = (PetscBool)(sA && sB && sG);
+    if (same && (MatB200HashInts(ad->j,ad->nz) != d->jhashA || MatB200HashInts(ao->j,ao->nz) != d->jhashB)) same = PETSC_FALSE;
     if (same) {                                                                   /* column-stripped blocks are not refreshed in place */
       int sa = 1,sb = 1;
       CHKB200(b200_mat_strips(d->mat,&sa,&sb));
@@ -373,6 +397,7 @@ static PetscErrorCode MatB200CopyToDevice_MPIAIJ(Mat A)
   ierr = PetscInfo2(A,"B200 device copy: full upload (%D + %D nonzeros) and ghost exchange plan\n",ad->nz,ao->nz);CHKERRQ(ierr);
   ierr = PetscFree3(d->iA,d->iB,d->garray);CHKERRQ(ierr);
   d->m = A->rmap->n; d->nzA = ad->nz; d->nzB = ao->nz; d->nghost = nghost;
+  d->jhashA = MatB200HashInts(ad->j,ad->nz); d->jhashB = MatB200HashInts(ao->j,ao->nz);
   ierr = PetscMalloc3(d->m+1,PetscInt,&d->iA,d->m+1,PetscInt,&d->iB,nghost+1,PetscInt,&d->garray);CHKERRQ(ierr);
   ierr = PetscMemcpy(d->iA,ad->i,(d->m+1)*sizeof(PetscInt));CHKERRQ(ierr);
   ierr = PetscMemcpy(d->iB,ao->i,(d->m+1)*sizeof(PetscInt));CHKERRQ(ierr);

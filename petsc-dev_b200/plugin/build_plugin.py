@@ -31,6 +31,8 @@ EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
     "vec_ex21": "src/vec/vec/examples/tests/ex21.c",
     # this repository's own driver (public PETSc API only): MatSetValuesBatch on the parallel type
     "b200_batch_mpiaij": os.path.join(ROOT, "tests", "c", "batch_mpiaij.c"),
+    # columns rewritten in place under unchanged row offsets (MatZeroRows): the device copy must notice
+    "b200_zerorows_refresh": os.path.join(ROOT, "tests", "c", "zerorows_refresh.c"),
 }
 
 

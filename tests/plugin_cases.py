@@ -48,6 +48,10 @@ CASES = {
     # MatSetValuesBatch on the parallel type (tests/c/batch_mpiaij.c: ex4's mesh through MatCreate/MatSetType(MATMPIAIJ))
     "batch_mpiaij": dict(prog="b200_batch_mpiaij", args=["-X", "6", "-Y", "5"], ref_args=["-mat_type", "mpiaij"],
                          b200_args=["-mat_type", "mpiaijb200", "-vec_type", "mpib200"]),
+    # tests/c/zerorows_refresh.c: MatZeroRows rewrites column indices in place, row offsets and nz unchanged
+    "zerorows_seqaij": dict(prog="b200_zerorows_refresh", args=[], ref_args=["-mat_type", "seqaij"], b200_args=["-mat_type", "seqaijb200", "-vec_type", "seqb200"]),
+    # (the parallel type's MatZeroRows sends every row to its owner, itself included, which MPIUNI cannot do: that case runs
+    # in the MPI flavour, tests/test_gpu_plugin_mpi.py)
     # src/mat/examples/tests/makefile:753,774,795
     "mat_ex5_11_A": dict(prog="mat_ex5", args=["-rectA"], ref_args=["-mat_type", "seqaij"], b200_args=["-mat_type", "seqaijb200", "-vec_type", "seqb200"],
                          golden="src/mat/examples/tests/output/ex5_11_A.out"),
