@@ -262,6 +262,10 @@ int b200_scatter_create(int nx_local, int ny,
                         int nto, const int *to_procs, const int *to_starts, const int *to_indices,
                         int nfrom, const int *from_procs, const int *from_starts, const int *from_indices,
                         int nlocal, const int *to_local, const int *from_local, b200_scatter *ctx);
+/* sequential -> sequential scatters (vscat.c:316-700: general/stride index sets on both sides, expanded to lists):
+ * forward y[dst_idx[i]] (+)= x[src_idx[i]], reverse x[src_idx[i]] (+)= y[dst_idx[i]]; repeated targets are applied in
+ * list order like the reference's loop.  Not collective. */
+int b200_scatter_create_local(int nx, int ny, int n, const int *src_idx, const int *dst_idx, b200_scatter *ctx);
 int b200_scatter_begin(b200_scatter ctx, double *x, double *y, int add, int reverse);
 int b200_scatter_end(b200_scatter ctx, double *x, double *y, int add, int reverse);
 int b200_scatter_destroy(b200_scatter ctx);

@@ -870,15 +870,21 @@ int b200_mpiaij_multtranspose(b200_mat A, const double *x, const double *yin, do
  * MPIAIJ operator uses (an operator-shaped object without matrix blocks): forward messages land contiguously in its
  * ghost vector and are then unpacked to from_indices; reverse messages land in its return buffer and are unpacked to
  * to_indices.  The self part (entries this rank owns) is a device copy done in Begin like vpscat.h:100-128. */
+/* A target list that names an entry more than once (ADD_VALUES into shared ghost points, or INSERT_VALUES where the last
+ * writer wins) is applied through a segment plan: entries grouped by target (stable, so positions ascend inside a
+ * group), one thread per distinct target, contributions taken in list order — the order of the reference's sequential
+ * loop `y[idx[i]] += v[i]` (vpscat.c:520-570, vscat.c:316-330).  No floating-point atomics: results are reproducible. */
+struct SegPlan { int nseg; int *d_target, *d_start, *d_pos; };
+
 struct b200_scatter_s {
   b200_mat ex;
   int      nx, ny, nrecv, nsend, nlocal;
   int     *d_from_indices, *d_to_local, *d_from_local;
   double  *d_stage;            /* [nrecv] reverse mode: y[from_indices] gathered before it travels                 */
-  bool     dup_from, dup_to, dup_local_from, dup_local_to;   /* repeated targets -> atomic adds               */
+  SegPlan  seg_from, seg_to, seg_local_from, seg_local_to;   /* nseg > 0: the list repeats targets               */
 };
 
-template <bool ADD, bool ATOMIC>
+template <bool ADD>
 __global__ void __launch_bounds__(256) scatter_store_kernel(int n, const int *__restrict__ dst_idx, const int *__restrict__ src_idx,
                                                             const double *__restrict__ src, double *dst)
 {
@@ -887,31 +893,73 @@ __global__ void __launch_bounds__(256) scatter_store_kernel(int n, const int *__
     const double v = src[src_idx ? __ldg(&src_idx[i]) : i];
     const int r = dst_idx ? __ldg(&dst_idx[i]) : i;
     if (!ADD) dst[r] = v;
-    else if (ATOMIC) atomicAdd(&dst[r], v);
     else dst[r] = dst[r] + v;
   }
 }
 
-static int scatter_store(int n, const int *dst_idx, const int *src_idx, const double *src, double *dst, bool add, bool atomic)
+template <bool ADD>
+__global__ void __launch_bounds__(256) scatter_seg_kernel(int nseg, const int *__restrict__ target, const int *__restrict__ start,
+                                                          const int *__restrict__ pos, const int *__restrict__ src_idx,
+                                                          const double *__restrict__ src, double *dst)
+{
+  const int stride = gridDim.x * blockDim.x;
+  for (int s = blockIdx.x * blockDim.x + threadIdx.x; s < nseg; s += stride) {
+    const int t = __ldg(&target[s]), e = __ldg(&start[s + 1]);
+    int k = ADD ? __ldg(&start[s]) : e - 1;                /* INSERT_VALUES: the last entry of the list wins       */
+    double acc = ADD ? dst[t] : 0.0;
+    for (; k < e; k++) {
+      const int i = __ldg(&pos[k]);
+      const double v = src[src_idx ? __ldg(&src_idx[i]) : i];
+      acc = ADD ? acc + v : v;
+    }
+    dst[t] = acc;
+  }
+}
+
+static int scatter_store(int n, const int *dst_idx, const int *src_idx, const double *src, double *dst, bool add, const SegPlan *seg)
 {
   if (n <= 0) return 0;
-  int g = (n + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
   cudaStream_t st = g_b200.stream;
-  if (!add) scatter_store_kernel<false, false><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
-  else if (atomic) scatter_store_kernel<true, true><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
-  else scatter_store_kernel<true, false><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
+  if (seg && seg->nseg > 0) {
+    int g = (seg->nseg + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
+    if (add) scatter_seg_kernel<true><<<g, 256, 0, st>>>(seg->nseg, seg->d_target, seg->d_start, seg->d_pos, src_idx, src, dst);
+    else scatter_seg_kernel<false><<<g, 256, 0, st>>>(seg->nseg, seg->d_target, seg->d_start, seg->d_pos, src_idx, src, dst);
+    B200_LAUNCHED(1);
+    return 0;
+  }
+  int g = (n + 255) / 256; if (g > B200_NSM * 4) g = B200_NSM * 4;
+  if (!add) scatter_store_kernel<false><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
+  else scatter_store_kernel<true><<<g, 256, 0, st>>>(n, dst_idx, src_idx, src, dst);
   B200_LAUNCHED(1);
   return 0;
 }
 
-static bool has_dups(const int *v, int n)
+/* builds the plan only when `tgt` repeats an entry (nseg stays 0 otherwise) */
+static int segplan_build(SegPlan *P, const int *tgt, int n)
 {
-  if (n < 2) return false;
-  std::vector<int> w(v, v + n);
-  std::sort(w.begin(), w.end());
-  for (int i = 1; i < n; i++) if (w[i] == w[i - 1]) return true;
-  return false;
+  P->nseg = 0; P->d_target = P->d_start = P->d_pos = NULL;
+  if (n < 2) return 0;
+  std::vector<int> pos((size_t)n);
+  for (int i = 0; i < n; i++) pos[i] = i;
+  std::stable_sort(pos.begin(), pos.end(), [tgt](int a, int b) { return tgt[a] < tgt[b]; });
+  bool dup = false;
+  for (int i = 1; i < n && !dup; i++) dup = tgt[pos[i]] == tgt[pos[i - 1]];
+  if (!dup) return 0;
+  std::vector<int> target, start;
+  for (int i = 0; i < n; i++) if (i == 0 || tgt[pos[i]] != tgt[pos[i - 1]]) { target.push_back(tgt[pos[i]]); start.push_back(i); }
+  start.push_back(n);
+  const int nseg = (int)target.size();
+  B200_CUDA(cudaMalloc((void **)&P->d_target, sizeof(int) * (size_t)nseg));
+  B200_CUDA(cudaMalloc((void **)&P->d_start, sizeof(int) * (size_t)(nseg + 1)));
+  B200_CUDA(cudaMalloc((void **)&P->d_pos, sizeof(int) * (size_t)n));
+  B200_CUDA(cudaMemcpy(P->d_target, target.data(), sizeof(int) * (size_t)nseg, cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemcpy(P->d_start, start.data(), sizeof(int) * (size_t)(nseg + 1), cudaMemcpyHostToDevice));
+  B200_CUDA(cudaMemcpy(P->d_pos, pos.data(), sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+  P->nseg = nseg;
+  return 0;
 }
+
+static void segplan_free(SegPlan *P) { cudaFree(P->d_target); cudaFree(P->d_start); cudaFree(P->d_pos); P->nseg = 0; P->d_target = P->d_start = P->d_pos = NULL; }
 
 extern "C" int b200_scatter_create(int nx_local, int ny,
                                    int nto, const int *to_procs, const int *to_starts, const int *to_indices,
@@ -945,11 +993,35 @@ extern "C" int b200_scatter_create(int nx_local, int ny,
   B200_CUDA(up(&S->d_to_local, to_local, nlocal));
   B200_CUDA(up(&S->d_from_local, from_local, nlocal));
   B200_CUDA(cudaMalloc((void **)&S->d_stage, sizeof(double) * (size_t)(nrecv + 2)));
-  S->dup_from = has_dups(from_indices, nrecv);
-  S->dup_local_from = has_dups(from_local, nlocal) || S->dup_from;
-  S->dup_local_to = has_dups(to_local, nlocal);
-  S->dup_to = false;
-  for (int k = 0; k < nto && !S->dup_to; k++) S->dup_to = has_dups(to_indices + to_starts[k], to_starts[k + 1] - to_starts[k]);
+  B200_CHK(segplan_build(&S->seg_from, from_indices, nrecv));
+  B200_CHK(segplan_build(&S->seg_local_from, from_local, nlocal));
+  B200_CHK(segplan_build(&S->seg_local_to, to_local, nlocal));
+  B200_CHK(segplan_build(&S->seg_to, to_indices, nsend));     /* over all neighbours: ascending rank, then list order */
+  *out = S;
+  return 0;
+}
+
+/* Sequential vector -> sequential vector (VecScatterCreate's SGtoSG / SGtoSS / SStoSG / SStoSS cases, vscat.c:316-700):
+ * y[dst_idx[i]] (+)= x[src_idx[i]], nothing travels, not collective. */
+extern "C" int b200_scatter_create_local(int nx, int ny, int n, const int *src_idx, const int *dst_idx, b200_scatter *out)
+{
+  B200_NEED_INIT();
+  if (!out) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
+  *out = NULL;
+  if (n < 0 || nx < 0 || ny < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative size");
+  for (int i = 0; i < n; i++)
+    if (src_idx[i] < 0 || src_idx[i] >= nx || dst_idx[i] < 0 || dst_idx[i] >= ny) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "local scatter index out of range");
+  b200_scatter S = (b200_scatter)calloc(1, sizeof(*S));
+  if (!S) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  S->nx = nx; S->ny = ny; S->nlocal = n;
+  B200_CUDA(cudaMalloc((void **)&S->d_to_local, sizeof(int) * (size_t)(n + 1)));
+  B200_CUDA(cudaMalloc((void **)&S->d_from_local, sizeof(int) * (size_t)(n + 1)));
+  if (n) {
+    B200_CUDA(cudaMemcpy(S->d_to_local, src_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMemcpy(S->d_from_local, dst_idx, sizeof(int) * (size_t)n, cudaMemcpyHostToDevice));
+  }
+  B200_CHK(segplan_build(&S->seg_local_from, dst_idx, n));
+  B200_CHK(segplan_build(&S->seg_local_to, src_idx, n));
   *out = S;
   return 0;
 }
@@ -957,8 +1029,9 @@ extern "C" int b200_scatter_create(int nx_local, int ny,
 extern "C" int b200_scatter_destroy(b200_scatter S)
 {
   if (!S) return 0;
-  b200_mat_destroy(S->ex);
+  if (S->ex) b200_mat_destroy(S->ex);
   cudaFree(S->d_from_indices); cudaFree(S->d_to_local); cudaFree(S->d_from_local); cudaFree(S->d_stage);
+  segplan_free(&S->seg_from); segplan_free(&S->seg_to); segplan_free(&S->seg_local_from); segplan_free(&S->seg_local_to);
   free(S);
   return 0;
 }
@@ -969,14 +1042,18 @@ extern "C" int b200_scatter_begin(b200_scatter S, double *x, double *y, int add,
 {
   B200_NEED_INIT();
   if (!S || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  if (!S->ex) {                                            /* sequential -> sequential: the whole scatter is the self part */
+    if (!reverse) return scatter_store(S->nlocal, S->d_from_local, S->d_to_local, x, y, add != 0, &S->seg_local_from);
+    return scatter_store(S->nlocal, S->d_to_local, S->d_from_local, y, x, add != 0, &S->seg_local_to);
+  }
   if (!reverse) {
     B200_CHK(b200_mpiaij_exchange_begin(S->ex, x));
-    return scatter_store(S->nlocal, S->d_from_local, S->d_to_local, x, y, add != 0, S->dup_local_from);
+    return scatter_store(S->nlocal, S->d_from_local, S->d_to_local, x, y, add != 0, &S->seg_local_from);
   }
-  B200_CHK(scatter_store(S->nrecv, NULL, S->d_from_indices, y, S->d_stage, false, false));     /* Pack: stage[i] = y[from_indices[i]] */
+  B200_CHK(scatter_store(S->nrecv, NULL, S->d_from_indices, y, S->d_stage, false, NULL));     /* Pack: stage[i] = y[from_indices[i]] */
   const double *buf = NULL;
   B200_CHK(reverse_begin(S->ex, S->d_stage, &buf));
-  return scatter_store(S->nlocal, S->d_to_local, S->d_from_local, y, x, add != 0, S->dup_local_to);
+  return scatter_store(S->nlocal, S->d_to_local, S->d_from_local, y, x, add != 0, &S->seg_local_to);
 }
 
 extern "C" int b200_scatter_end(b200_scatter S, double *x, double *y, int add, int reverse)
@@ -984,17 +1061,16 @@ extern "C" int b200_scatter_end(b200_scatter S, double *x, double *y, int add, i
   B200_NEED_INIT();
   if (!S || !x || !y) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   b200_mat E = S->ex;
+  if (!E) return 0;
   if (!reverse) {
     B200_CHK(b200_mpiaij_exchange_end(E));
     if (g_b200.size <= 1 && !E->peerplan) return 0;
-    return scatter_store(S->nrecv, S->d_from_indices, NULL, E->d_lvec[E->epoch & 1], y, add != 0, S->dup_from);
+    return scatter_store(S->nrecv, S->d_from_indices, NULL, E->d_lvec[E->epoch & 1], y, add != 0, &S->seg_from);
   }
   if (g_b200.size <= 1 && !E->peerplan) return 0;
   B200_CHK(reverse_wait(E));
   const double *buf = E->peerplan ? ((PeerPlan *)E->peerplan)->rbuf[E->repoch & 1] : E->d_sendbuf;
-  for (int k = 0; k < E->nto; k++) {                      /* neighbour by neighbour, ascending rank: fixed summation order */
-    const int len = E->to_starts[k + 1] - E->to_starts[k];
-    B200_CHK(scatter_store(len, E->d_to_indices + E->to_starts[k], NULL, buf + E->to_starts[k], x, add != 0, S->dup_to));
-  }
-  return 0;
+  /* one pass over every neighbour's message: entries several neighbours contribute to are summed by the segment plan in
+     ascending rank order (the reference takes them in MPI_Waitany arrival order, vpscat.h:200-216) */
+  return scatter_store(S->nsend, E->d_to_indices, NULL, buf, x, add != 0, &S->seg_to);
 }

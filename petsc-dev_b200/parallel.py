@@ -325,3 +325,12 @@ def set_values_batch_mpiaij(rank, size, ranges, N, nl, elem_rows, elem_mats, bs=
     host = setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=bs, dist=dist, device=device)
     A = create_mpiaij(host)
     return (A, (ai, aj, aa)) if return_host else A
+
+
+def create_scatter_local(nx, ny, src_idx, dst_idx):
+    """VecScatterCreate between two sequential vectors (vscat.c:1030-1260), index sets already expanded to lists:
+    forward y[dst_idx[i]] (+)= x[src_idx[i]].  Not collective."""
+    s, d = _i32(src_idx), _i32(dst_idx)
+    h = C.c_void_p()
+    _chk(lib.b200_scatter_create_local(int(nx), int(ny), int(s.size), _ip(s), _ip(d), C.byref(h)), "VecScatterCreate")
+    return Scatter(h, int(nx), int(ny))

@@ -12,7 +12,13 @@ static PetscBool PetscB200Registered = PETSC_FALSE;
 #define __FUNCT__ "PetscB200Finalize"
 static PetscErrorCode PetscB200Finalize(void)
 {
+  PetscInt       h2d,d2h,sdev,shost;
+  PetscErrorCode ierr;
+
   PetscFunctionBegin;
+  ierr = PetscB200GetCounters(&h2d,&d2h,PETSC_NULL,PETSC_NULL);CHKERRQ(ierr);
+  ierr = PetscB200GetScatterCounters(&sdev,&shost);CHKERRQ(ierr);
+  ierr = PetscInfo4(0,"B200 totals: %D vector uploads, %D vector downloads, %D scatters on the device, %D through the host\n",h2d,d2h,sdev,shost);CHKERRQ(ierr);
   PetscB200Registered = PETSC_FALSE;
   PetscFunctionReturn(0);
 }

@@ -7,8 +7,11 @@
  * reference counts so -log_summary stays comparable (SURVEY 8(b) "Logging obligations").
  *
  * Coherence: `where` says which copy is current.  Host access goes through ops->getarray (petscnative is FALSE), which
- * copies back when the device is newer and marks the host newer (a VecGetArrayRead cannot be told apart from a write
- * access on this seam, vecimpl.h:382,395).  Inherited host ops that read `->array` directly (VecSetValues_Seq, VecView,
+ * copies back when the device is newer.  VecGetArrayRead and VecGetArray reach the same op (vecimpl.h:382,411), but
+ * only VecRestoreArray bumps the object state (vecimpl.h:430-432 against :395-401): getarray records the state and
+ * leaves both copies valid; the next access of any kind compares — an unchanged state means the host only read, and
+ * the device copy is still current (no re-upload after a VecGetArrayRead, the read/write distinction the CUSP seam has
+ * through valid_GPU_array, vecimpl.h:375-379,410-414).  Inherited host ops that read `->array` directly (VecSetValues_Seq, VecView,
  * VecMax ...) are wrapped so that they see current data.  The host array is pinned and allocated lazily (KSP work
  * vectors never get one), as VecCUSPAllocateCheckHost does (veccusp.cu:34-60). */
 #include "petscb200plugin.h"
@@ -21,6 +24,8 @@ typedef struct {
   PetscScalar  *d;         /* device array, map->n entries                                  */
   PetscScalar  *pinned;    /* the lazily allocated pinned host array (also VECHEADER.array) */
   B200VecWhere  where;
+  PetscBool     hostpending; /* the host array was handed out while both copies were current ...               */
+  PetscInt      hoststate;   /* ... at this object state: a changed state since means it was written (below)  */
 } B200VecData;
 
 typedef struct { Vec_Seq base; B200VecData dev; } Vec_SeqB200;
@@ -43,6 +48,16 @@ PETSC_STATIC_INLINE PetscErrorCode VecB200Data(Vec v,B200VecData **dev)
   else if (v->ops->destroy == VecDestroy_MPIB200) *dev = &((Vec_MPIB200*)v->data)->dev;
   else SETERRQ1(((PetscObject)v)->comm,PETSC_ERR_ARG_WRONG,"Vector of type %s where a B200 vector is needed",((PetscObject)v)->type_name);
   PetscFunctionReturn(0);
+}
+
+/* settle a pending host hand-out: state moved on => someone called VecRestoreArray (or changed the vector through the
+ * host some other way) => the host copy is the newer one.  Called first thing by every access. */
+PETSC_STATIC_INLINE void VecB200ResolveHostAccess(Vec v,B200VecData *dev)
+{
+  if (dev->hostpending) {
+    dev->hostpending = PETSC_FALSE;
+    if (dev->where == B200_VEC_BOTH && ((PetscObject)v)->state != dev->hoststate) dev->where = B200_VEC_HOST;
+  }
 }
 
 /* ---- allocation and the two copies ---------------------------------------------------------------------------- */
@@ -117,6 +132,7 @@ PetscErrorCode VecB200GetDeviceRead(Vec v,const PetscScalar **a)
 
   PetscFunctionBegin;
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  VecB200ResolveHostAccess(v,dev);
   ierr = VecB200CopyToDevice(v,dev);CHKERRQ(ierr);
   if (dev->where == B200_VEC_UNALLOCATED) {
     CHKB200(b200_vec_set(v->map->n,dev->d,0.0));
@@ -135,6 +151,7 @@ PetscErrorCode VecB200GetDeviceWrite(Vec v,PetscScalar **a)
 
   PetscFunctionBegin;
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  dev->hostpending = PETSC_FALSE;
   ierr = VecB200AllocateCheck(v,dev);CHKERRQ(ierr);
   dev->where = B200_VEC_DEVICE;
   *a = dev->d;
@@ -166,6 +183,7 @@ PetscErrorCode VecB200GetWhere(Vec v,B200VecWhere *w)
 
   PetscFunctionBegin;
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  VecB200ResolveHostAccess(v,dev);
   *w = dev->where;
   PetscFunctionReturn(0);
 }
@@ -192,6 +210,7 @@ static PetscErrorCode VecB200HostReadWrite(Vec v)
 
   PetscFunctionBegin;
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  VecB200ResolveHostAccess(v,dev);
   ierr = VecB200CopyFromDevice(v,dev);CHKERRQ(ierr);
   dev->where = B200_VEC_HOST;
   PetscFunctionReturn(0);
@@ -207,18 +226,26 @@ static PetscErrorCode VecB200HostRead(Vec v)
 
   PetscFunctionBegin;
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  VecB200ResolveHostAccess(v,dev);
   ierr = VecB200CopyFromDevice(v,dev);CHKERRQ(ierr);
   PetscFunctionReturn(0);
 }
 
+/* VecGetArray AND VecGetArrayRead (vecimpl.h:382,411): current data on the host; whether the caller writes shows in the
+ * object state at the next access (VecRestoreArray increases it, VecRestoreArrayRead does not) */
 #undef __FUNCT__
 #define __FUNCT__ "VecGetArray_B200"
 static PetscErrorCode VecGetArray_B200(Vec v,PetscScalar **a)
 {
+  B200VecData    *dev;
   PetscErrorCode ierr;
 
   PetscFunctionBegin;
-  ierr = VecB200HostReadWrite(v);CHKERRQ(ierr);
+  ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
+  VecB200ResolveHostAccess(v,dev);
+  ierr = VecB200CopyFromDevice(v,dev);CHKERRQ(ierr);
+  if (dev->where == B200_VEC_BOTH) { dev->hostpending = PETSC_TRUE; dev->hoststate = ((PetscObject)v)->state; }
+  else dev->where = B200_VEC_HOST;
   *a = ((Vec_Seq*)v->data)->array;
   PetscFunctionReturn(0);
 }
@@ -589,7 +616,7 @@ static PetscErrorCode NAME PROTO { PetscErrorCode ierr; PetscFunctionBegin; ierr
  * since we know it does not write, the state from before the call is put back */
 #define HOSTOP_RO(NAME,BASE,PROTO,ARGS) \
 static PetscErrorCode NAME PROTO { PetscErrorCode ierr; B200VecData *dev; B200VecWhere w; PetscFunctionBegin; ierr = VecB200HostRead(x);CHKERRQ(ierr); \
-  ierr = VecB200Data(x,&dev);CHKERRQ(ierr); w = dev->where; ierr = BASE ARGS;CHKERRQ(ierr); dev->where = w; PetscFunctionReturn(0); }
+  ierr = VecB200Data(x,&dev);CHKERRQ(ierr); w = dev->where; ierr = BASE ARGS;CHKERRQ(ierr); dev->where = w; dev->hostpending = PETSC_FALSE; PetscFunctionReturn(0); }
 
 #undef __FUNCT__
 #define __FUNCT__ "VecHostOp_B200"
@@ -646,7 +673,7 @@ static PetscErrorCode VecMaxPointwiseDivide_SeqB200(Vec x,Vec y,PetscReal *max)
   ierr = VecB200Data(x,&dx);CHKERRQ(ierr); wx = dx->where;
   ierr = VecB200Data(y,&dy);CHKERRQ(ierr); wy = dy->where;
   ierr = VecMaxPointwiseDivide_Seq(x,y,max);CHKERRQ(ierr);
-  dx->where = wx; dy->where = wy;
+  dx->where = wx; dy->where = wy; dx->hostpending = dy->hostpending = PETSC_FALSE;
   PetscFunctionReturn(0);
 }
 

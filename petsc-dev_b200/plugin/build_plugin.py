@@ -33,6 +33,10 @@ EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
     "b200_batch_mpiaij": os.path.join(ROOT, "tests", "c", "batch_mpiaij.c"),
     # columns rewritten in place under unchanged row offsets (MatZeroRows): the device copy must notice
     "b200_zerorows_refresh": os.path.join(ROOT, "tests", "c", "zerorows_refresh.c"),
+    # VecScatter layouts between option-typed vectors (the device scatter behind PETSc's VecScatter object)
+    "b200_scatter_cases": os.path.join(ROOT, "tests", "c", "scatter_cases.c"),
+    # VecGetArrayRead between device operations: one download, no upload
+    "b200_coherence_seam": os.path.join(ROOT, "tests", "c", "coherence_seam.c"),
 }
 
 
@@ -98,6 +102,13 @@ def build_flavour(name, verbose=True):
         subprocess.run(cmd, check=True)
         if verbose:
             print("built", plugin)
+    # the VecScatterCreate interposer (LD_PRELOAD): attaches the device scatter to every scatter an unmodified PETSc creates
+    hook, hooksrc = os.path.join(fl["plugdir"], "libpetscb200scatterhook.so"), os.path.join(HERE, "b200scatterhook.c")
+    if os.path.exists(hooksrc) and newer(hook, [hooksrc, plugin]):
+        subprocess.run(["gcc", "-shared", "-fPIC", "-O2", "-w"] + inc(fl) + [hooksrc, "-o", hook, "-L", fl["plugdir"], "-lpetscb200plugin",
+                        "-L", fl["refdir"], "-l" + fl["reflib"], "-L", LIBDIR] + fl["extra_libs"] + rp + ["-ldl"], check=True)
+        if verbose:
+            print("built", hook)
     examples = dict(EXAMPLES)
     if name == "mpi":
         examples.update(MPI_EXAMPLES)

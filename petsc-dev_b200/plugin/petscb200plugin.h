@@ -51,6 +51,13 @@ extern PetscErrorCode VecB200GetDeviceWrite(Vec, PetscScalar **);      /* conten
 extern PetscErrorCode VecB200GetDeviceReadWrite(Vec, PetscScalar **);
 extern PetscErrorCode VecB200GetWhere(Vec, B200VecWhere *);
 extern PetscErrorCode MatB200GetHandle(Mat, void **b200_mat_handle);   /* device operator of an aijb200 matrix, refreshed */
+/* PETSc's VecScatter object on the device (b200scatter.c): after this call VecScatterBegin/End of `ctx` run GPU to GPU
+ * whenever both vectors are B200 vectors and fall through to the reference's code otherwise.  The seam is the one
+ * VecScatterInitializeForGPU uses (ctx->spptr, src/vec/vec/utils/veccusp/vscatcusp.c:29).  A PETSc with the plugin built
+ * in would call it at the end of VecScatterCreate (vscat.c:920); for an unmodified PETSc,
+ * LD_PRELOAD=libpetscb200scatterhook.so does exactly that (b200scatterhook.c). */
+extern PetscErrorCode VecScatterB200Attach(VecScatter ctx);
+extern PetscErrorCode PetscB200GetScatterCounters(PetscInt *ondevice, PetscInt *onhost);
 /* counters for tests: host<->device copies the coherence protocol performed, device matrix uploads */
 extern PetscErrorCode PetscB200GetCounters(PetscInt *h2d, PetscInt *d2h, PetscInt *matuploads, PetscInt *matvalueupdates);
 

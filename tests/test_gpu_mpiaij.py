@@ -72,9 +72,54 @@ def test_scatter_single_rank_self_part(gpu, P):
     S.scatter(x, y, add=True)
     assert np.array_equal(y.get_array(), yh + xh[inidx])
     y.set_array(yh)
-    S.scatter(x, y, add=True, reverse=True)                # repeated targets (3 and 7 twice) -> atomic adds
-    want = xh.copy(); np.add.at(want, inidx, yh)
-    assert np.allclose(x.get_array(), want, rtol=0, atol=1e-15)
+    S.scatter(x, y, add=True, reverse=True)                # repeated targets (3 and 7 twice): segment plan, list order
+    want = xh.copy()
+    for i, t in enumerate(inidx):                          # the reference's loop x[idx[i]] += y[i] (vpscat.c:520-570)
+        want[t] = want[t] + yh[i]
+    assert np.array_equal(x.get_array(), want)             # bit-exact and reproducible: no floating-point atomics
+    first = x.get_array().copy()
+    for _ in range(3):
+        x.set_array(xh)
+        S.scatter(x, y, add=True, reverse=True)
+        assert np.array_equal(x.get_array(), first)
+    x.set_array(xh)
+    S.scatter(x, y, add=False, reverse=True)               # INSERT with repeated targets: the last entry of the list wins
+    want = xh.copy()
+    for i, t in enumerate(inidx):
+        want[t] = yh[i]
+    assert np.array_equal(x.get_array(), want)
     with pytest.raises(gpu.PetscB200Error) as e:
         par.create_scatter(0, 1, ranges, np.array([1], np.int32), np.array([9], np.int32), ny)
     assert e.value.code == 63
+
+
+def test_sequential_scatter_layouts(gpu):
+    """b200_scatter_create_local: y[dst[i]] (+)= x[src[i]] and its reverse, repeated targets in list order
+    (VecScatterBegin_SGToSG, vscat.c:344-376)."""
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    rng = np.random.default_rng(5)
+    nx, ny, n = 4000, 3000, 10000
+    src = rng.integers(0, nx, n).astype(np.int32)
+    dst = rng.integers(0, ny, n).astype(np.int32)          # many targets named several times
+    S = par.create_scatter_local(nx, ny, src, dst)
+    xh, yh = rng.standard_normal(nx), rng.standard_normal(ny)
+    x, y = gpu.Vec(nx, xh), gpu.Vec(ny, yh)
+    S.scatter(x, y, add=True)
+    want = yh.copy()
+    for i in range(n):
+        want[dst[i]] = want[dst[i]] + xh[src[i]]
+    assert np.array_equal(y.get_array(), want)
+    y.set_array(yh)
+    S.scatter(x, y)
+    want = yh.copy()
+    for i in range(n):
+        want[dst[i]] = xh[src[i]]
+    assert np.array_equal(y.get_array(), want)
+    y.set_array(yh)
+    S.scatter(x, y, add=True, reverse=True)
+    want = xh.copy()
+    for i in range(n):
+        want[src[i]] = want[src[i]] + yh[dst[i]]
+    assert np.array_equal(x.get_array(), want)
+    with pytest.raises(gpu.PetscB200Error):
+        par.create_scatter_local(nx, ny, np.array([nx], np.int32), np.array([0], np.int32))

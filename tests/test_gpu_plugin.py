@@ -151,3 +151,16 @@ def test_parallel_matsetvaluesbatch_takes_the_device_path():
     gold = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_goldens.json")))["ksp_ex4_0"]["rows"]
     want = [("row %d: %s" % (r, " ".join("(%d, %g) " % (cc, v) for cc, v in row))).strip() for r, row in enumerate(gold)]
     assert matview_rows(out) == want, out
+
+
+def test_read_access_does_not_invalidate_the_device_copy():
+    """tests/c/coherence_seam.c: two VecGetArrayRead passes between device operations and one VecGetArray write — the
+    plugin's -info totals must show 2 downloads and exactly 1 upload (the write), and the numbers must be the reference's."""
+    want = run("b200_coherence_seam", [])
+    got = run("b200_coherence_seam", ["-dll_prepend", PLUGIN, "-vec_type", "b200", "-info"])
+    m = re.search(r"B200 totals: (\d+) vector uploads, (\d+) vector downloads", got)
+    assert m, got[-1500:]
+    assert (int(m.group(1)), int(m.group(2))) == (1, 2), m.group(0)
+    plain = "\n".join(l for l in got.splitlines() if not l.startswith("["))
+    same_text(plain, want)
+    assert "after the write: norm1 23" in want
