@@ -78,6 +78,8 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
   int       *d_longstart;     /* [nlong+1] first chunk slot of each long row                                          */
   double    *d_longpart;      /* [nchunks] per-chunk partial sums                                                     */
   double    *d_dotpart;       /* [grid + nlong] per-CTA partials of the fused x.y                                    */
+  int       *d_diagpos;       /* [m] position of a_ii in d_a or -1 (Mat_SeqAIJ::diag, aij.c:1486 MatMarkDiagonal_SeqAIJ);
+                                 recorded by the first MatGetDiagonal, kept across value-only refreshes               */
   /* column strips (cache blocking for matrices whose x gathers would not stay in L2): when nstrips > 1 the block is
    * stored as nstrips CSR blocks over disjoint column ranges (global column ids kept) and the product is
    * y = S_0 x; y += S_1 x; ...  — for one lane per row the row sum is still one left-to-right chain */

@@ -64,22 +64,31 @@ __global__ void zero_rows_kernel(int n, double *y)
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) y[i] = 0.0;
 }
 
-/* d[i] = a_ii or 0 (MatGetDiagonal_SeqAIJ aij.c:1040-1073); columns ascending -> bisection */
+/* later calls: d[i] = a[diagpos[i]] (MatGetDiagonal_SeqAIJ with the marks of MatMarkDiagonal_SeqAIJ, aij.c:1040-1073,1486) */
+__global__ void __launch_bounds__(256) diag_gather_kernel(int r0, int m, const int *__restrict__ pos, const double *__restrict__ aa, double *__restrict__ d)
+{
+  const int stride = gridDim.x * blockDim.x;
+  for (int i = r0 + blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) { const int p = __ldg(&pos[i]); d[i] = p >= 0 ? __ldg(&aa[p]) : 0.0; }
+}
+
+/* d[i] = a_ii or 0 (MatGetDiagonal_SeqAIJ aij.c:1040-1073); columns ascending -> bisection; the position found is kept */
 __global__ void diag_kernel(int r0, int m, const int *__restrict__ ai, const int *__restrict__ aj, const double *__restrict__ aa,
-                            int coloff, double *__restrict__ d)
+                            int coloff, double *__restrict__ d, int *__restrict__ pos)
 {
   const int stride = gridDim.x * blockDim.x;
   for (int i = r0 + blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
     int lo = ai[i], hi = ai[i + 1];
     const int want = i + coloff;
     double v = 0.0;
+    int at = -1;
     while (lo < hi) {
       const int mid = (lo + hi) >> 1;
       const int c = aj[mid];
-      if (c == want) { v = aa[mid]; break; }
+      if (c == want) { v = aa[mid]; at = mid; break; }
       if (c < want) lo = mid + 1; else hi = mid;
     }
     d[i] = v;
+    pos[i] = at;
   }
 }
 
@@ -94,7 +103,7 @@ void b200_seq_free(B200Seq *S)
   }
   if (S->d_ci && S->d_ci != S->d_i) cudaFree(S->d_ci);
   cudaFree(S->d_i); cudaFree(S->d_j); cudaFree(S->d_a); cudaFree(S->d_rindex);
-  cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
+  cudaFree(S->d_diagpos); cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
   memset(S, 0, sizeof(*S));
 }
 
@@ -721,13 +730,23 @@ extern "C" int b200_mat_get_diagonal(b200_mat A, double *d)
       if (r0 >= r1) continue;
       const B200Seq *C = &S->strips[k];
       int g = (r1 - r0 + 255) / 256; if (g > B200_NSM * 8) g = B200_NSM * 8;
-      diag_kernel<<<g, 256, 0, g_b200.stream>>>(r0, r1, C->d_i, C->d_j, C->d_a, 0, d);
+      B200Seq *Cw = &A->A.strips[k];
+      /* the strip keeps positions for its own rows r0..r1 only (indexed by the global row: pointer shifted by r0) */
+      if (Cw->d_diagpos) diag_gather_kernel<<<g, 256, 0, g_b200.stream>>>(r0, r1, C->d_diagpos - r0, C->d_a, d);
+      else {
+        B200_CUDA(cudaMalloc((void **)&Cw->d_diagpos, sizeof(int) * (size_t)(r1 - r0 + 1)));
+        diag_kernel<<<g, 256, 0, g_b200.stream>>>(r0, r1, C->d_i, C->d_j, C->d_a, 0, d, Cw->d_diagpos - r0);
+      }
       B200_LAUNCHED(1);
     }
     return 0;
   }
   int g = (S->m + 255) / 256; if (g > B200_NSM * 8) g = B200_NSM * 8;
-  diag_kernel<<<g, 256, 0, g_b200.stream>>>(0, S->m, S->d_i, S->d_j, S->d_a, 0, d);
+  if (S->d_diagpos) diag_gather_kernel<<<g, 256, 0, g_b200.stream>>>(0, S->m, S->d_diagpos, S->d_a, d);
+  else {
+    B200_CUDA(cudaMalloc((void **)&A->A.d_diagpos, sizeof(int) * (size_t)(S->m + 1)));
+    diag_kernel<<<g, 256, 0, g_b200.stream>>>(0, S->m, S->d_i, S->d_j, S->d_a, 0, d, A->A.d_diagpos);
+  }
   B200_LAUNCHED(1);
   return 0;
 }

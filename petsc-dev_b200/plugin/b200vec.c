@@ -100,6 +100,7 @@ static PetscErrorCode VecB200CopyToDevice(Vec v,B200VecData *dev)       /* VecCU
     CHKB200(b200_memcpy_h2d(dev->d,((Vec_Seq*)v->data)->array,sizeof(PetscScalar)*(size_t)v->map->n));
     b200_h2d_count++;
     dev->where = B200_VEC_BOTH;
+    ierr = PetscInfo1(v,"B200 vector upload (%D entries)\n",v->map->n);CHKERRQ(ierr);
   }
   PetscFunctionReturn(0);
 }
@@ -116,6 +117,7 @@ static PetscErrorCode VecB200CopyFromDevice(Vec v,B200VecData *dev)     /* VecCU
     CHKB200(b200_memcpy_d2h(((Vec_Seq*)v->data)->array,dev->d,sizeof(PetscScalar)*(size_t)v->map->n));
     b200_d2h_count++;
     dev->where = B200_VEC_BOTH;
+    ierr = PetscInfo1(v,"B200 vector download (%D entries)\n",v->map->n);CHKERRQ(ierr);
   } else if (dev->where == B200_VEC_UNALLOCATED) {
     ierr = PetscMemzero(((Vec_Seq*)v->data)->array,sizeof(PetscScalar)*(size_t)v->map->n);CHKERRQ(ierr);
     dev->where = B200_VEC_HOST;
@@ -154,6 +156,9 @@ PetscErrorCode VecB200GetDeviceWrite(Vec v,PetscScalar **a)
   dev->hostpending = PETSC_FALSE;
   ierr = VecB200AllocateCheck(v,dev);CHKERRQ(ierr);
   dev->where = B200_VEC_DEVICE;
+  /* what VecRestoreArray does for the host loops (vecimpl.h:430) and VecCUSPRestoreArrayWrite for the CUSP type: callers
+     outside the Vec front ends (MatMult in 3.3 does not touch y's state, matrix.c:2154) must still invalidate cached norms */
+  ierr = PetscObjectStateIncrease((PetscObject)v);CHKERRQ(ierr);
   *a = dev->d;
   PetscFunctionReturn(0);
 }
@@ -170,6 +175,7 @@ PetscErrorCode VecB200GetDeviceReadWrite(Vec v,PetscScalar **a)
   ierr = VecB200GetDeviceRead(v,&r);CHKERRQ(ierr);
   ierr = VecB200Data(v,&dev);CHKERRQ(ierr);
   dev->where = B200_VEC_DEVICE;
+  ierr = PetscObjectStateIncrease((PetscObject)v);CHKERRQ(ierr);
   *a = (PetscScalar*)r;
   PetscFunctionReturn(0);
 }

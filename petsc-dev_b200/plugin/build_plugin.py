@@ -106,7 +106,7 @@ def build_flavour(name, verbose=True):
     hook, hooksrc = os.path.join(fl["plugdir"], "libpetscb200scatterhook.so"), os.path.join(HERE, "b200scatterhook.c")
     if os.path.exists(hooksrc) and newer(hook, [hooksrc, plugin]):
         subprocess.run(["gcc", "-shared", "-fPIC", "-O2", "-w"] + inc(fl) + [hooksrc, "-o", hook, "-L", fl["plugdir"], "-lpetscb200plugin",
-                        "-L", fl["refdir"], "-l" + fl["reflib"], "-L", LIBDIR] + fl["extra_libs"] + rp + ["-ldl"], check=True)
+                        "-L", fl["refdir"], "-l" + fl["reflib"], "-L", LIBDIR] + fl["extra_libs"] + ["-Wl,-rpath,$ORIGIN"] + rp + ["-ldl"], check=True)
         if verbose:
             print("built", hook)
     examples = dict(EXAMPLES)

@@ -43,6 +43,9 @@ def _check(gpu, R, P, m, n, ip, j, a, seed=2, exact=True, lanes=-1, park=-1, lon
         d = gpu.Vec(m)
         A.get_diagonal(d)
         assert np.array_equal(d.get_array(), ref.diagonal())
+        d.set_array(np.full(m, -7.0))
+        A.get_diagonal(d)                                 # second call: gather through the recorded positions
+        assert np.array_equal(d.get_array(), ref.diagonal())
     assert A.flops() == 2.0 * len(a) - np.count_nonzero(np.diff(ip))
     return A
 

@@ -35,7 +35,12 @@ def launch(np_, prog, args):
         pytest.fail("MPI flavour not built (oracle/build_ref.py --mpi, petsc-dev_b200/plugin/build_plugin.py)")
     r = subprocess.run([MPIEXEC, "-n", str(np_), exe] + args, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
-    return r.stdout
+    return drop_nccl_banner(r.stdout)
+
+
+def drop_nccl_banner(out):
+    """NCCL prints its version on stdout when the box sets NCCL_DEBUG=VERSION: not program output"""
+    return "\n".join(l for l in out.splitlines() if not l.startswith("NCCL version")) + "\n"
 
 
 def need(np_):
@@ -55,8 +60,9 @@ def test_zerorows_rewrites_columns_in_place(np_):
     want = launch(np_, "b200_zerorows_refresh", args + ["-mat_type", "mpiaij"])
     got = launch(np_, "b200_zerorows_refresh", args + B200 + ["-info"])
     # one rank: MATAIJB200 resolves to the sequential type (MatRegisterBaseName, matreg.c:170), same decision there
+    # PetscInfo on an object prints from the first rank of the object's communicator only
     mine = [l for l in got.splitlines() if "MatB200CopyToDevice_" in l]
-    assert sum("full upload" in l for l in mine) == 2 * np_ and not any("values refreshed" in l for l in mine), mine
+    assert sum("full upload" in l for l in mine) == 2 and not any("values refreshed" in l for l in mine), mine
     plain = "\n".join(l for l in got.splitlines() if not l.startswith("["))          # -info lines start with "[rank]"
     same_text(plain, want)
     assert "after MatZeroRows" in want
@@ -129,7 +135,7 @@ def launch_hooked(np_, prog, args):
     env = dict(os.environ, LD_PRELOAD=HOOK)
     r = subprocess.run([MPIEXEC, "-n", str(np_), exe] + args, capture_output=True, text=True, timeout=600, env=env)
     assert r.returncode == 0, (r.stdout[-2000:], r.stderr[-3000:])
-    return r.stdout
+    return drop_nccl_banner(r.stdout)
 
 
 def scatter_totals(out):
