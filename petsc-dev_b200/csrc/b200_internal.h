@@ -49,6 +49,9 @@ extern B200Ctx g_b200;
 int  b200_seterr(int code, const char *fmt, ...);
 int  b200_cuda_err(cudaError_t e, const char *what, const char *file, int line);
 bool b200_ready(void);
+/* host -> device copy of a large pageable array through parallel pinned staging (b200_runtime.cu); synchronous */
+int  b200_upload_pageable(void *dst, const void *src, size_t bytes);
+void b200_upload_release(void);
 
 #define B200_CUDA(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) return b200_cuda_err(e__, #call, __FILE__, __LINE__); } while (0)
 #define B200_CHK(call)  do { int r__ = (call); if (r__) return r__; } while (0)

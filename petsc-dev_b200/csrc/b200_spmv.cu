@@ -228,13 +228,13 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
 
   const size_t pad = 8;
   B200_CUDA(cudaMalloc((void **)&S->d_i, sizeof(int) * ((size_t)m + 1)));
-  B200_CUDA(cudaMemcpy(S->d_i, i, sizeof(int) * ((size_t)m + 1), cudaMemcpyHostToDevice));
+  B200_CHK(b200_upload_pageable(S->d_i, i, sizeof(int) * ((size_t)m + 1)));
   if (!adopt) {
     B200_CUDA(cudaMalloc((void **)&S->d_j, sizeof(int) * ((size_t)nz + pad)));
     B200_CUDA(cudaMalloc((void **)&S->d_a, sizeof(double) * ((size_t)nz + pad)));
     if (nz) {
-      B200_CUDA(cudaMemcpy(S->d_j, j, sizeof(int) * (size_t)nz, cudaMemcpyHostToDevice));
-      B200_CUDA(cudaMemcpy(S->d_a, a, sizeof(double) * (size_t)nz, cudaMemcpyHostToDevice));
+      B200_CHK(b200_upload_pageable(S->d_j, j, sizeof(int) * (size_t)nz));
+      B200_CHK(b200_upload_pageable(S->d_a, a, sizeof(double) * (size_t)nz));
     }
   }
   B200_CUDA(cudaMemset(S->d_j + nz, 0, sizeof(int) * pad));
@@ -553,9 +553,7 @@ extern "C" int b200_mat_update_values(b200_mat A, const double *a)
   if (A->kind != 0) return b200_seterr(B200_ERR_SUP, "value refresh is implemented for the sequential type");
   if (A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "value refresh is not implemented for a column-stripped matrix (recreate it)");
   if (A->A.T) { b200_seq_free(A->A.T); free(A->A.T); A->A.T = NULL; }        /* rebuilt from the new values on demand */
-  B200_CUDA(cudaMemcpyAsync(A->A.d_a, a, sizeof(double) * (size_t)A->A.nz, cudaMemcpyHostToDevice, g_b200.stream));
-  B200_CUDA(cudaStreamSynchronize(g_b200.stream));
-  return 0;
+  return b200_upload_pageable(A->A.d_a, a, sizeof(double) * (size_t)A->A.nz);
 }
 
 extern "C" int b200_mat_update_values_mpiaij(b200_mat A, const double *ad, const double *ao)
@@ -569,9 +567,8 @@ extern "C" int b200_mat_update_values_mpiaij(b200_mat A, const double *ad, const
   const double *src[2] = {ad, ao};
   for (int k = 0; k < 2; k++) {
     if (blk[k]->T) { b200_seq_free(blk[k]->T); free(blk[k]->T); blk[k]->T = NULL; }   /* rebuilt from the new values on demand */
-    if (blk[k]->nz) B200_CUDA(cudaMemcpyAsync(blk[k]->d_a, src[k], sizeof(double) * (size_t)blk[k]->nz, cudaMemcpyHostToDevice, g_b200.stream));
+    if (blk[k]->nz) B200_CHK(b200_upload_pageable(blk[k]->d_a, src[k], sizeof(double) * (size_t)blk[k]->nz));
   }
-  B200_CUDA(cudaStreamSynchronize(g_b200.stream));
   return 0;
 }
 
