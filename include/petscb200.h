@@ -290,6 +290,10 @@ typedef struct {
   int    check_every;        /* fused CG only: host looks at the device-side convergence flag every k iterations */
   int    gmres_modified_gs;  /* 1 = modified Gram-Schmidt (borthog.c:30-52: one VecDot + VecAXPY per basis vector)
                                 instead of the default classical one (borthog2.c:35-118); -ksp_gmres_modifiedgramschmidt */
+  const double *pc_jacobi_inverse_diag;   /* device vector or NULL.  NULL: PCJACOBI is set up from the matrix diagonal
+                                (jacobi.c:160-190, default variant).  Otherwise the inverse diagonal the caller's PC already
+                                holds — the plugin passes PCApply(pc, ones), so -pc_jacobi_rowmax/_rowsum/_abs mean what
+                                they mean in the reference                                                            */
 } b200_ksp_options;
 int b200_ksp_default_options(b200_ksp_options *o);
 typedef struct {

@@ -254,7 +254,8 @@ class KSPOptions(C.Structure):
     _fields_ = [("ksp_type", C.c_int), ("pc_type", C.c_int), ("rtol", C.c_double), ("abstol", C.c_double),
                 ("dtol", C.c_double), ("max_it", C.c_int), ("norm_type", C.c_int), ("guess_nonzero", C.c_int),
                 ("gmres_restart", C.c_int), ("gmres_cgs_refine", C.c_int), ("gmres_haptol", C.c_double),
-                ("fused", C.c_int), ("check_every", C.c_int), ("gmres_modified_gs", C.c_int)]
+                ("fused", C.c_int), ("check_every", C.c_int), ("gmres_modified_gs", C.c_int),
+                ("pc_jacobi_inverse_diag", C.c_void_p)]
 
 
 class Mat:

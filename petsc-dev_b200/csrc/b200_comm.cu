@@ -46,8 +46,10 @@ struct NcclApi {
 };
 static NcclApi g_nccl = {};
 
+struct ArenaRange { size_t off, len; };
 struct B200P2P {
-  size_t bytes, bump;                    /* arena size, bump-allocator offset                                       */
+  size_t bytes, bump;                    /* arena size, end of the part handed out so far                           */
+  ArenaRange *freelist; int nfree, capfree;   /* returned ranges below `bump`, sorted by offset, neighbours merged  */
   char  *arena;                          /* this rank's arena                                                       */
   char  *peer[B200_MAX_RANKS];           /* every rank's arena as mapped here ([rank] == arena)                     */
   unsigned long long ar_seq;             /* allreduce sequence number (same on all ranks: collective calls)        */
@@ -116,6 +118,7 @@ extern "C" int b200_comm_destroy(void)
     if (g_b200.nccl && g_b200.size > 1) b200_comm_barrier();        /* nobody may still be storing into an arena */
     for (int r = 0; r < g_b200.size; r++) if (r != g_b200.rank && P->peer[r]) cudaIpcCloseMemHandle(P->peer[r]);
     cudaFree(P->d_inbox); cudaFree(P->arena);
+    free(P->freelist);
     free(P);
     g_b200.peer = NULL;
   }
@@ -180,13 +183,51 @@ bool b200_p2p_next(unsigned long long *seq, unsigned long long *const **inbox)
   return true;
 }
 
+/* Arena ranges (256-byte granules): first fit in the list of returned ranges, else from the top.  Matrices and scatters
+ * come and go in any order (every attached VecScatter owns a range), so a range goes back to the list on destroy;
+ * neighbours merge, and a range ending at `bump` lowers it.  Purely local bookkeeping: ranks exchange the offsets they
+ * chose (peerplan_build), they need not choose the same ones. */
 static int p2p_alloc(size_t bytes, size_t *off)
 {
   B200P2P *P = g_b200.peer;
+  bytes = (bytes + 255) & ~(size_t)255;
+  for (int k = 0; k < P->nfree; k++)
+    if (P->freelist[k].len >= bytes) {
+      *off = P->freelist[k].off;
+      P->freelist[k].off += bytes; P->freelist[k].len -= bytes;
+      if (!P->freelist[k].len) { memmove(P->freelist + k, P->freelist + k + 1, sizeof(ArenaRange) * (size_t)(P->nfree - k - 1)); P->nfree--; }
+      return 0;
+    }
   const size_t a = (P->bump + 255) & ~(size_t)255;
   if (a + bytes > P->bytes) return 1;
   *off = a; P->bump = a + bytes;
   return 0;
+}
+
+static void p2p_free(size_t off, size_t bytes)
+{
+  B200P2P *P = g_b200.peer;
+  if (!P || !bytes) return;
+  bytes = (bytes + 255) & ~(size_t)255;
+  if (P->nfree == P->capfree) {
+    const int cap = P->capfree ? 2 * P->capfree : 16;
+    ArenaRange *q = (ArenaRange *)realloc(P->freelist, sizeof(ArenaRange) * (size_t)cap);
+    if (!q) return;                                        /* the range stays lost; nothing else breaks */
+    P->freelist = q; P->capfree = cap;
+  }
+  int k = 0;
+  while (k < P->nfree && P->freelist[k].off < off) k++;
+  memmove(P->freelist + k + 1, P->freelist + k, sizeof(ArenaRange) * (size_t)(P->nfree - k));
+  P->freelist[k].off = off; P->freelist[k].len = bytes; P->nfree++;
+  if (k + 1 < P->nfree && P->freelist[k].off + P->freelist[k].len == P->freelist[k + 1].off) {
+    P->freelist[k].len += P->freelist[k + 1].len;
+    memmove(P->freelist + k + 1, P->freelist + k + 2, sizeof(ArenaRange) * (size_t)(P->nfree - k - 2)); P->nfree--;
+  }
+  if (k > 0 && P->freelist[k - 1].off + P->freelist[k - 1].len == P->freelist[k].off) {
+    P->freelist[k - 1].len += P->freelist[k].len;
+    memmove(P->freelist + k, P->freelist + k + 1, sizeof(ArenaRange) * (size_t)(P->nfree - k - 1)); P->nfree--;
+  }
+  if (P->nfree && P->freelist[P->nfree - 1].off + P->freelist[P->nfree - 1].len == P->bump) { P->bump = P->freelist[P->nfree - 1].off; P->nfree--; }
 }
 
 extern "C" int b200_comm_enable_p2p(int enable)
@@ -361,9 +402,8 @@ static void peerplan_free(b200_mat M)
 {
   PeerPlan *pp = (PeerPlan *)M->peerplan;
   if (!pp) return;
-  B200P2P *P = g_b200.peer;
   cudaFree(pp->d_blob); cudaFree(pp->d_ticket); cudaFree(pp->d_blob_rev); cudaFree(pp->d_ticket_rev);
-  if (P && P->bump == pp->arena_hi) P->bump = pp->arena_lo;      /* last one in: give the arena range back          */
+  p2p_free(pp->arena_lo, pp->arena_hi - pp->arena_lo);            /* back to the arena's free list, whatever the order */
   free(pp);
   M->peerplan = NULL;
   M->d_lvec[0] = M->d_lvec[1] = NULL;                             /* they lived in the arena                          */
@@ -411,13 +451,15 @@ static int peerplan_build(b200_mat M)
   enum { OK = 0, LV0, LV1, FLG, CRD, RB0, RB1, RFLG, RCRD, RECV0 };
   const int W = RECV0 + 2 * B200_MAX_RANKS;
   long long mine[RECV0 + 2 * B200_MAX_RANKS], all[B200_MAX_RANKS][RECV0 + 2 * B200_MAX_RANKS];
-  const size_t lo = P->bump;
   size_t off[RECV0] = {0};
   const size_t want[RECV0] = {0, sizeof(double) * (size_t)(nghost + 2), sizeof(double) * (size_t)(nghost + 2), 8 * (size_t)R, 8 * (size_t)R,
                               sizeof(double) * (size_t)(nsend + 2), sizeof(double) * (size_t)(nsend + 2), 8 * (size_t)R, 8 * (size_t)R};
-  int fail = 0;
-  for (int k = 1; k < RECV0 && !fail; k++) fail = p2p_alloc(want[k], &off[k]);
-  const size_t hi = P->bump;
+  /* one range for everything this operator keeps in the arena */
+  size_t total = 0, lo = 0;
+  for (int k = 1; k < RECV0; k++) { off[k] = total; total += (want[k] + 255) & ~(size_t)255; }
+  const int fail = p2p_alloc(total, &lo);
+  const size_t hi = lo + total;
+  for (int k = 1; k < RECV0; k++) off[k] += lo;
   mine[OK] = fail ? 0 : 1;
   for (int k = 1; k < RECV0; k++) mine[k] = (long long)off[k];
   for (int r = 0; r < 2 * R; r++) mine[RECV0 + r] = -1;
@@ -435,11 +477,17 @@ static int peerplan_build(b200_mat M)
   }
   bool ok = true;
   for (int r = 0; r < size; r++) ok = ok && all[r][OK] == 1;
-  if (!ok) { P->bump = lo; return 1; }                            /* every rank sees the same table -> same decision  */
-  for (int k = 0; k < nto; k++)
-    if (all[M->to_procs[k]][RECV0 + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not expect the entries rank %d sends", M->to_procs[k], rank);
-  for (int k = 0; k < nfrom; k++)
-    if (all[M->from_procs[k]][RECV0 + R + rank] < 0) return b200_seterr(B200_ERR_PLIB, "rank %d does not send to rank %d what it expects", M->from_procs[k], rank);
+  if (!ok) { if (!fail) p2p_free(lo, total); return 1; }          /* every rank sees the same table -> same decision  */
+  /* the lists must mirror each other; every rank checks the WHOLE table, so all of them reach the same verdict and none
+     is left alone in the closing barrier */
+  for (int r = 0; r < size; r++)
+    for (int q = 0; q < size; q++) {
+      const bool sends = all[r][RECV0 + R + q] >= 0, expects = all[q][RECV0 + r] >= 0;
+      if (sends != expects) {
+        p2p_free(lo, total);
+        return b200_seterr(B200_ERR_PLIB, sends ? "rank %d does not expect the entries rank %d sends" : "rank %d expects entries rank %d does not send", q, r);
+      }
+    }
   for (int k = 1; k < RECV0; k++) B200_CUDA(cudaMemsetAsync(P->arena + off[k], 0, want[k], c.stream));
   PeerPlan *pp = (PeerPlan *)calloc(1, sizeof(PeerPlan));
   if (!pp) return b200_seterr(B200_ERR_MEM, "out of host memory");

@@ -44,11 +44,15 @@ __global__ void jacobi_fix_kernel(int n, double *d)
   }
 }
 
-static int pc_setup(Pc *pc, b200_mat A, int type)
+static int pc_setup(Pc *pc, b200_mat A, int type, const double *inverse_diag_dev)
 {
   pc->type = type; pc->n = A->A.m; pc->d = NULL;
   if (type == 1) {
     B200_CHK(b200_malloc(sizeof(double) * (size_t)(pc->n + 2), (void **)&pc->d));
+    if (inverse_diag_dev) {                                  /* the caller's PCJACOBI has been set up already (any variant) */
+      if (pc->n) B200_CHK(b200_vec_copy(pc->n, inverse_diag_dev, pc->d));
+      return 0;
+    }
     B200_CHK(b200_mat_get_diagonal(A, pc->d));
     if (pc->n) {
       int g = (pc->n + 255) / 256; if (g > B200_NSM * 8) g = B200_NSM * 8;
@@ -257,7 +261,7 @@ __global__ void __launch_bounds__(256) cg_pupdate_kernel(int n, const CgState *_
 /* x += a p ; r -= a w ; z = r .* d (or z = r) ; partial sums of z.z, z.r, r.r  — 5 reads + 3 writes per row */
 template <bool JACOBI, bool INLINE_AFTER>
 __global__ void __launch_bounds__(512) cg_update_kernel(int n, CgState *s, double *__restrict__ x, const double *__restrict__ p,
-                                                        double *__restrict__ r, const double *__restrict__ w, double *__restrict__ z,
+                                                        double *__restrict__ r, const double *w, double *z,   /* W == Z (cg.c:121): no restrict */
                                                         const double *__restrict__ d, double *partials, unsigned *ticket, double *hist,
                                                         const CgAr ar)
 {
@@ -724,7 +728,7 @@ extern "C" int b200_ksp_solve(b200_mat A, const b200_ksp_options *o, const doubl
   const int n = A->A.m;
   memset(result, 0, sizeof(*result));
   Pc pc;
-  B200_CHK(pc_setup(&pc, A, o->pc_type));                       /* KSPSetUp -> PCSetUp (itfunc.c:267) */
+  B200_CHK(pc_setup(&pc, A, o->pc_type, o->pc_jacobi_inverse_diag));                      /* KSPSetUp -> PCSetUp (itfunc.c:267) */
   Conv cv;
   cv.rtol = o->rtol; cv.abstol = o->abstol; cv.dtol = o->dtol; cv.rnorm0 = 0; cv.ttol = 0;
   cv.normtype = o->norm_type; cv.guess_nonzero = o->guess_nonzero;

@@ -48,6 +48,7 @@ static PetscErrorCode KSPSolve_B200(KSP ksp)
   PetscScalar       *x;
   double            *hist;
   PetscInt          k,histmax;
+  Vec               ones = 0,dinv = 0;
   PetscErrorCode    ierr;
 
   PetscFunctionBegin;
@@ -57,6 +58,7 @@ static PetscErrorCode KSPSolve_B200(KSP ksp)
   ierr = PetscObjectTypeCompare((PetscObject)ksp->pc,PCNONE,&isnone);CHKERRQ(ierr);
   if (!isjacobi && !isnone) SETERRQ1(((PetscObject)ksp)->comm,PETSC_ERR_SUP,"KSP B200 types support -pc_type jacobi or none, not %s",((PetscObject)ksp->pc)->type_name);
   if (ksp->pc_side != PC_LEFT) SETERRQ(((PetscObject)ksp)->comm,PETSC_ERR_SUP,"KSP B200 types support left preconditioning only");
+  if (ksp->transpose_solve) SETERRQ(((PetscObject)ksp)->comm,PETSC_ERR_SUP,"KSP B200 types do not support KSPSolveTranspose");
   if (ksp->dscale || ksp->nullsp) SETERRQ(((PetscObject)ksp)->comm,PETSC_ERR_SUP,"KSP B200 types do not support diagonal scaling or null spaces");
   /* KSPDefaultConverged only (the convergence test runs on the device); -ksp_converged_use_initial_residual_norm etc. refused */
   isdefault = (ksp->converged == KSPDefaultConverged) ? PETSC_TRUE : PETSC_FALSE;
@@ -82,8 +84,18 @@ static PetscErrorCode KSPSolve_B200(KSP ksp)
   ierr = VecB200GetDeviceRead(ksp->vec_rhs,&b);CHKERRQ(ierr);
   if (ksp->guess_zero) { ierr = VecB200GetDeviceWrite(ksp->vec_sol,&x);CHKERRQ(ierr); }
   else                 { ierr = VecB200GetDeviceReadWrite(ksp->vec_sol,&x);CHKERRQ(ierr); }
+  if (isjacobi) {
+    /* the inverse diagonal comes from the PC itself, which KSPSetUp has set up (itfunc.c:267): PCApply_Jacobi on a vector
+       of ones (jacobi.c:266-278) is exactly jac->diag, whichever of -pc_jacobi_rowmax/_rowsum/_abs built it (jacobi.c:125-206) */
+    ierr = VecDuplicate(ksp->vec_rhs,&ones);CHKERRQ(ierr);
+    ierr = VecDuplicate(ksp->vec_rhs,&dinv);CHKERRQ(ierr);
+    ierr = VecSet(ones,1.0);CHKERRQ(ierr);
+    ierr = PCApply(ksp->pc,ones,dinv);CHKERRQ(ierr);
+    ierr = VecB200GetDeviceRead(dinv,&o.pc_jacobi_inverse_diag);CHKERRQ(ierr);
+  }
   CHKB200(b200_ksp_solve(A,&o,b,x,hist,(int)histmax,&res));
-  ierr = PetscObjectStateIncrease((PetscObject)ksp->vec_sol);CHKERRQ(ierr);
+  ierr = VecDestroy(&ones);CHKERRQ(ierr);
+  ierr = VecDestroy(&dinv);CHKERRQ(ierr);
 
   /* replay the residual history through the reference's bookkeeping (kspimpl.h:131 KSPLogResidualHistory, KSPMonitor) */
   ierr = PetscObjectTakeAccess(ksp);CHKERRQ(ierr);

@@ -39,6 +39,11 @@ CASES = {
                                   ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
     "ksp_ex2_gmresb200_refine": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "19", "-n", "27", "-pc_type", "jacobi", "-ksp_gmres_cgs_refinement_type", "refine_always"],
                                      ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
+    # PCJACOBI variants (jacobi.c:125-206): the device drivers take the inverse diagonal from the PC itself
+    "ksp_ex2_cgb200_rowsum": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "23", "-n", "19", "-pc_type", "jacobi", "-pc_jacobi_rowsum"],
+                                  ref_args=["-ksp_type", "cg"], b200_args=B200 + ["-ksp_type", "cgb200"], history=True),
+    "ksp_ex2_gmresb200_rowmax": dict(prog="ksp_ex2", args=["-ksp_monitor", "-m", "17", "-n", "22", "-pc_type", "jacobi", "-pc_jacobi_rowmax", "-pc_jacobi_abs"],
+                                     ref_args=["-ksp_type", "gmres"], b200_args=B200 + ["-ksp_type", "gmresb200"], history=True),
     # src/ksp/ksp/examples/tutorials/makefile:410 — two systems, same nonzero structure, different values: the second
     # assembly reaches the device as a value-only refresh (no re-binning, no new exchange plan)
     "ksp_ex5_1": dict(prog="ksp_ex5", args=["-pc_type", "jacobi", "-ksp_monitor_short", "-ksp_gmres_cgs_refinement_type", "refine_always"],

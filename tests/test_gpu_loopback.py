@@ -112,3 +112,24 @@ def test_transpose_and_general_scatter_on_the_loopback(gpu, loop, R, P):
     want = R.RefMat(m, m, *d["full"], no_inode=True).multtranspose(xh)
     assert np.all(np.abs(z.get_array() - want) <= 1e-12 * 12.0)
     A.destroy()
+
+
+def test_arena_ranges_return_in_any_order(gpu, loop, R, P):
+    """Operators (and attached VecScatters) are destroyed in any order: every range goes back to the peer arena's free list
+    and is reused, so a long create/destroy sequence never falls back to the NCCL transport (is_fused stays true) and the
+    products stay bit-exact.  The arena is 512 MiB; 600 operators of ~1 MiB each would not fit without reuse."""
+    keep = []
+    for rep in range(600):
+        d, A = _operator(loop, P, 128, 128, 3 + rep % 3, fused=True)     # ghost vectors of 2 x 128 x 128 entries, 2 parities, 2 directions
+        assert loop.is_fused(A)[0], "operator %d fell off the peer transport: the arena leaks" % rep
+        keep.append((d, A))
+        if len(keep) == 3:
+            keep.pop(rep % 2)[1].destroy()                               # not the most recent one
+    d, A = keep[-1]
+    m = d["m"]
+    xh = P.random_vector(m, 5)
+    x, z = gpu.Vec(m, xh), gpu.Vec(m)
+    A.mult(x, z)
+    assert np.array_equal(z.get_array(), _oracle(R, d, xh))
+    for _, B in keep:
+        B.destroy()
