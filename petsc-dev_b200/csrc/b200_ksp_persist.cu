@@ -89,24 +89,50 @@ __device__ __forceinline__ double cta_sum_strided(const double *v, int n, int st
   return u;
 }
 
-template <int G, int THREADS, int TILE_NNZ>
+/* three interleaved sums v[3 i + q] at once (same fixed order per sum as cta_sum_strided); results valid in thread 0 */
+template <int THREADS>
+__device__ __forceinline__ void cta_sum3(const double *v, int n, double (*s_w)[THREADS / 32], double (&out)[3])
+{
+  double t[3] = {0.0, 0.0, 0.0};
+  for (int i = threadIdx.x; i < n; i += THREADS) {
+#pragma unroll
+    for (int q = 0; q < 3; q++) t[q] += __ldcg(&v[(size_t)i * 3 + q]);
+  }
+#pragma unroll
+  for (int q = 0; q < 3; q++) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t[q] += __shfl_xor_sync(0xffffffffu, t[q], o);
+  }
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) { s_w[0][threadIdx.x >> 5] = t[0]; s_w[1][threadIdx.x >> 5] = t[1]; s_w[2][threadIdx.x >> 5] = t[2]; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+#pragma unroll
+    for (int q = 0; q < 3; q++) { double u = 0.0; for (int w = 0; w < THREADS / 32; w++) u += s_w[q][w]; out[q] = u; }
+  }
+}
+
+template <int G, int THREADS, int TILE_NNZ, int STAGES>
 __global__ void __launch_bounds__(THREADS)
 cg_persistent_kernel(const CgPersistArgs a)
 {
   constexpr int SE = TILE_NNZ + SPMV_ALIGN_PAD;
   extern __shared__ __align__(128) unsigned char spmv_smem[];
   double   *s_a  = reinterpret_cast<double *>(spmv_smem);
-  int      *s_j  = reinterpret_cast<int *>(spmv_smem + (size_t)SE * 8);
-  uint64_t *bars = reinterpret_cast<uint64_t *>(spmv_smem + (size_t)SE * 12);
+  int      *s_j  = reinterpret_cast<int *>(spmv_smem + (size_t)STAGES * SE * 8);
+  uint64_t *bars = reinterpret_cast<uint64_t *>(spmv_smem + (size_t)STAGES * SE * 12);
   __shared__ double s_w[3][THREADS / 32];
 
   const int tid = threadIdx.x, r = tid / G, g = tid % G;
   const int nblk = gridDim.x, stride = gridDim.x;
   const int n = a.n, n2 = n >> 1;
   uint64_t pol = 0;
-  uint32_t nwait = 0;                                /* tiles this CTA has consumed so far: mbarrier phase parity */
+  uint32_t nwait[STAGES];                            /* tiles consumed so far from each stage: mbarrier phase parity */
+#pragma unroll
+  for (int q = 0; q < STAGES; q++) nwait[q] = 0;
   if (tid == 0) {
-    b200_mbar_init(&bars[0], 1);
+#pragma unroll
+    for (int q = 0; q < STAGES; q++) b200_mbar_init(&bars[q], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     /* a matrix that fits in L2 next to the vectors is re-read from there every iteration: do not mark it evict-first */
@@ -114,13 +140,13 @@ cg_persistent_kernel(const CgPersistArgs a)
     else pol = b200_policy_evict_first();
   }
   __syncthreads();
-  auto issue = [&](int4 d) {                        /* thread 0 only */
+  auto issue = [&](int q, int4 d) {                 /* thread 0 only */
     const int ka = d.z & ~3, kb = (d.w + 3) & ~3;
     const uint32_t nn = (uint32_t)(kb - ka);
-    if (nn == 0) { b200_mbar_expect_tx(&bars[0], 0); return; }
-    b200_mbar_expect_tx(&bars[0], nn * 12u);
-    b200_bulk_g2s(s_a, a.aa + ka, nn * 8u, &bars[0], pol);
-    b200_bulk_g2s(s_j, a.aj + ka, nn * 4u, &bars[0], pol);
+    if (nn == 0) { b200_mbar_expect_tx(&bars[q], 0); return; }
+    b200_mbar_expect_tx(&bars[q], nn * 12u);
+    b200_bulk_g2s(s_a + (size_t)q * SE, a.aa + ka, nn * 8u, &bars[q], pol);
+    b200_bulk_g2s(s_j + (size_t)q * SE, a.aj + ka, nn * 4u, &bars[q], pol);
   };
   CgState *s = a.s;
   unsigned gen;
@@ -159,16 +185,22 @@ cg_persistent_kernel(const CgPersistArgs a)
     {
       double dot = 0.0;
       int t = blockIdx.x;
-      if (tid == 0 && t < a.ntiles) issue(__ldg(&a.tiles[t]));
-      for (; t < a.ntiles; t += stride) {
+      if (tid == 0) {
+#pragma unroll
+        for (int q = 0; q < STAGES; q++) if (t + q * stride < a.ntiles) issue(q, __ldg(&a.tiles[t + q * stride]));
+      }
+      for (int it = 0; t < a.ntiles; t += stride, it++) {
+        const int q = it % STAGES;
         const int4 dsc = __ldg(&a.tiles[t]);
         int b0 = 0, e0 = 0, row = -1;
         if (r < dsc.y - dsc.x) { row = dsc.x + r; b0 = __ldg(&a.ai[row]); e0 = __ldg(&a.ai[row + 1]); }
-        b200_mbar_wait(&bars[0], nwait & 1u);
-        nwait++;
+        uint32_t par = 0;
+#pragma unroll
+        for (int u = 0; u < STAGES; u++) if (u == q) { par = nwait[u] & 1u; nwait[u]++; }
+        b200_mbar_wait(&bars[q], par);
         const int ka = dsc.z & ~3;
-        const double *sa = s_a - ka;
-        const int    *sj = s_j - ka;
+        const double *sa = s_a + (size_t)q * SE - ka;
+        const int    *sj = s_j + (size_t)q * SE - ka;
         double sum = 0.0;
         if (G == 1) {
 #pragma unroll 4
@@ -182,7 +214,7 @@ cg_persistent_kernel(const CgPersistArgs a)
         }
         if (g == 0 && row >= 0) { a.zw[row] = sum; dot += __ldcg(&a.p[row]) * sum; }
         __syncthreads();
-        if (tid == 0 && t + stride < a.ntiles) issue(__ldg(&a.tiles[t + stride]));
+        if (tid == 0 && t + STAGES * stride < a.ntiles) issue(q, __ldg(&a.tiles[t + STAGES * stride]));
       }
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
@@ -239,8 +271,7 @@ cg_persistent_kernel(const CgPersistArgs a)
     }
     if (grid_arrive(a.bar, nblk, &gen)) {
       double red[3];
-#pragma unroll
-      for (int q = 0; q < 3; q++) red[q] = cta_sum_strided<THREADS>(a.partials + q, nblk, 3, s_w[0]);
+      cta_sum3<THREADS>(a.partials, nblk, s_w, red);     /* one pass for the three sums: the other CTAs are waiting */
       if (tid == 0) {
         s->red[0] = red[0]; s->red[1] = red[1]; s->red[2] = red[2];
         cg_after_update_body(s, a.hist);              /* cg.c:227-281 and the top of the next iteration */
@@ -252,15 +283,16 @@ cg_persistent_kernel(const CgPersistArgs a)
 
 /* ------------------------------------------------------------------------------------------------ host */
 typedef void (*persist_kern_t)(const CgPersistArgs);
+#define PERSIST_STAGES 2                               /* the next tile streams in while this one is summed */
 static persist_kern_t persist_kernel(int G)
 {
   switch (G) {
-    case 1:  return cg_persistent_kernel<1, 256, 2048>;
-    case 2:  return cg_persistent_kernel<2, 256, 2048>;
-    case 4:  return cg_persistent_kernel<4, 256, 2048>;
-    case 8:  return cg_persistent_kernel<8, 256, 2048>;
-    case 16: return cg_persistent_kernel<16, 256, 2048>;
-    default: return cg_persistent_kernel<32, 256, 2048>;
+    case 1:  return cg_persistent_kernel<1, 256, 2048, PERSIST_STAGES>;
+    case 2:  return cg_persistent_kernel<2, 256, 2048, PERSIST_STAGES>;
+    case 4:  return cg_persistent_kernel<4, 256, 2048, PERSIST_STAGES>;
+    case 8:  return cg_persistent_kernel<8, 256, 2048, PERSIST_STAGES>;
+    case 16: return cg_persistent_kernel<16, 256, 2048, PERSIST_STAGES>;
+    default: return cg_persistent_kernel<32, 256, 2048, PERSIST_STAGES>;
   }
 }
 
@@ -287,14 +319,17 @@ int b200_cg_persistent_run(b200_mat A, int jacobi, const double *d, double *X, d
   B200Ctx &c = g_b200;
   const B200Seq *S = &A->A;
   persist_kern_t k = persist_kernel(S->G);
-  const size_t smem = SpmvSmem<256, 2048, 1>::BYTES;
+  const size_t smem = SpmvSmem<256, 2048, PERSIST_STAGES>::BYTES;
   static int occ_cache[33] = {0};
   if (!occ_cache[S->G]) {
     B200_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int o = 0;
     B200_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, k, 256, smem));
     if (o < 1) return b200_seterr(B200_ERR_LIB, "persistent CG kernel does not fit on an SM");
-    occ_cache[S->G] = o > 4 ? 4 : o;                  /* 4 x 256 lanes per SM: fewer CTAs make cheaper barriers */
+    int cap = 4;                                      /* 4 x 256 lanes per SM: fewer CTAs make cheaper barriers */
+    const char *eo = getenv("B200_CG_PERSIST_OCC");
+    if (eo && atoi(eo) > 0) cap = atoi(eo);
+    occ_cache[S->G] = o > cap ? cap : o;
   }
   int grid = c.nsm * occ_cache[S->G];
   if (!g_bar) {
@@ -305,6 +340,7 @@ int b200_cg_persistent_run(b200_mat A, int jacobi, const double *d, double *X, d
   memset(&a, 0, sizeof(a));
   a.n = S->m; a.ntiles = S->ntiles; a.iters = iters; a.jacobi = jacobi;
   a.keep_l2 = (12.0 * (double)S->nz + 48.0 * (double)S->m) <= 100e6;
+  { const char *ek = getenv("B200_CG_PERSIST_KEEPL2"); if (ek) a.keep_l2 = atoi(ek) != 0; }
   a.tiles = S->d_tiles; a.ai = S->d_i; a.aj = S->d_j; a.aa = S->d_a;
   a.x = X; a.r = R; a.zw = ZW; a.p = P; a.d = d; a.s = ds;
   a.dotpart = c.d_partials; a.partials = c.d_partials + B200_RED_MAXBLK; a.hist = dhist; a.bar = g_bar;

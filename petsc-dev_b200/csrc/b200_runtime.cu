@@ -253,39 +253,47 @@ extern "C" int b200_memset(void *dst, int byte, size_t bytes)
 #include <vector>
 #include <atomic>
 
-#define B200_UP_CHUNK   ((size_t)8 << 20)
+#define B200_UP_CHUNK   ((size_t)4 << 20)
 #define B200_UP_MAXW    8
-struct UpWorker { cudaStream_t st; void *buf[2]; cudaEvent_t ev[2]; cudaEvent_t done; };
+#define B200_UP_MIN     ((size_t)64 << 20)     /* below this one ordinary copy is as fast as setting the pipeline up */
+struct UpWorker { cudaStream_t st; void *buf[2]; cudaEvent_t ev[2]; bool ready; };
 static UpWorker g_up[B200_UP_MAXW];
-static int      g_up_n = 0;
+static int      g_up_max = 0;
 
-static int up_init(void)
+/* workers are set up one by one as uploads need them (pinning host memory is slow: ~8 MB per worker, a few ms each) */
+static int up_worker_init(int k)
 {
-  if (g_up_n) return 0;
-  int w = (int)std::thread::hardware_concurrency() / 2;
-  const char *e = getenv("B200_UPLOAD_THREADS");
-  if (e && atoi(e) > 0) w = atoi(e);
-  if (w < 1) w = 1;
-  if (w > B200_UP_MAXW) w = B200_UP_MAXW;
-  for (int k = 0; k < w; k++) {
-    B200_CUDA(cudaStreamCreateWithFlags(&g_up[k].st, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; b++) {
-      B200_CUDA(cudaHostAlloc(&g_up[k].buf[b], B200_UP_CHUNK, cudaHostAllocDefault));
-      B200_CUDA(cudaEventCreateWithFlags(&g_up[k].ev[b], cudaEventDisableTiming));
-    }
-    B200_CUDA(cudaEventCreateWithFlags(&g_up[k].done, cudaEventDisableTiming));
+  if (g_up[k].ready) return 0;
+  B200_CUDA(cudaStreamCreateWithFlags(&g_up[k].st, cudaStreamNonBlocking));
+  for (int b = 0; b < 2; b++) {
+    B200_CUDA(cudaHostAlloc(&g_up[k].buf[b], B200_UP_CHUNK, cudaHostAllocDefault));
+    B200_CUDA(cudaEventCreateWithFlags(&g_up[k].ev[b], cudaEventDisableTiming));
   }
-  g_up_n = w;
+  g_up[k].ready = true;
   return 0;
+}
+
+static int up_workers_for(size_t bytes)
+{
+  if (!g_up_max) {
+    int w = (int)std::thread::hardware_concurrency() / 2;
+    const char *e = getenv("B200_UPLOAD_THREADS");
+    if (e && atoi(e) > 0) w = atoi(e);
+    g_up_max = w < 1 ? 1 : (w > B200_UP_MAXW ? B200_UP_MAXW : w);
+  }
+  size_t w = bytes / ((size_t)32 << 20);                   /* one worker per 32 MB, so a 100 MB matrix pins little */
+  if (w < 2) w = 2;
+  return w > (size_t)g_up_max ? g_up_max : (int)w;
 }
 
 void b200_upload_release(void)
 {
-  for (int k = 0; k < g_up_n; k++) {
-    cudaStreamDestroy(g_up[k].st); cudaEventDestroy(g_up[k].done);
+  for (int k = 0; k < B200_UP_MAXW; k++) {
+    if (!g_up[k].ready) continue;
+    cudaStreamDestroy(g_up[k].st);
     for (int b = 0; b < 2; b++) { cudaFreeHost(g_up[k].buf[b]); cudaEventDestroy(g_up[k].ev[b]); }
+    g_up[k].ready = false;
   }
-  g_up_n = 0;
 }
 
 int b200_upload_pageable(void *dst, const void *src, size_t bytes)
@@ -295,14 +303,14 @@ int b200_upload_pageable(void *dst, const void *src, size_t bytes)
   cudaPointerAttributes at;
   const bool pinned = cudaPointerGetAttributes(&at, src) == cudaSuccess && (at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged);
   cudaGetLastError();
-  if (pinned || bytes < 4 * B200_UP_CHUNK) {                /* small, or already pinned: one ordinary copy */
+  if (pinned || bytes < B200_UP_MIN) {                      /* small, or already pinned: one ordinary copy */
     B200_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c.stream));
     B200_CUDA(cudaStreamSynchronize(c.stream));
     return 0;
   }
-  B200_CHK(up_init());
   const size_t nchunks = (bytes + B200_UP_CHUNK - 1) / B200_UP_CHUNK;
-  const int W = (size_t)g_up_n < nchunks ? g_up_n : (int)nchunks;
+  const int W = up_workers_for(bytes);
+  for (int w = 0; w < W; w++) B200_CHK(up_worker_init(w));
   std::atomic<int> err(0);
   const int device = c.device;
   /* the destination may still be in use by work queued on the compute stream (a value refresh of a live matrix) */
@@ -319,7 +327,6 @@ int b200_upload_pageable(void *dst, const void *src, size_t bytes)
       if (cudaMemcpyAsync((char *)dst + off, u.buf[b], len, cudaMemcpyHostToDevice, u.st) != cudaSuccess) { err = 1; return; }
       if (cudaEventRecord(u.ev[b], u.st) != cudaSuccess) { err = 1; return; }
     }
-    if (cudaEventRecord(u.done, u.st) != cudaSuccess) err = 1;
   };
   std::vector<std::thread> th;
   for (int w = 1; w < W; w++) th.emplace_back(work, w);
