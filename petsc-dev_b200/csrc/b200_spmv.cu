@@ -112,6 +112,15 @@ void b200_seq_free(B200Seq *S)
 static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a, bool adopt = false)
 {
   memset(S, 0, sizeof(*S));
+  {
+    static bool gather_mode_set = false;
+    if (!gather_mode_set) {
+      const char *e = getenv("B200_SPMV_GATHER_CG");
+      const int v = e ? atoi(e) : 0;
+      B200_CUDA(cudaMemcpyToSymbol(b200_c_gather_cg, &v, sizeof(int)));
+      gather_mode_set = true;
+    }
+  }
   if (adopt) { S->d_j = const_cast<int *>(j); S->d_a = const_cast<double *>(a); }   /* owned from here on, also on failure */
   if (m < 0 || n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative matrix size %d x %d", m, n);
   if (!i || i[0] != 0) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets must start at 0");
@@ -224,6 +233,7 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   S->ntiles = (int)tiles.size();
   S->nlong  = (int)longrows.size();
   S->grid   = g_b200.nsm * g_cfgs[S->cfg].ctas_per_sm;
+  { const char *eg = getenv("B200_SPMV_CTAS"); if (eg && atoi(eg) > 0) S->grid = g_b200.nsm * atoi(eg); }   /* experiment: fewer resident CTAs per SM */
   if (S->grid > S->ntiles) S->grid = S->ntiles;
 
   const size_t pad = 8;

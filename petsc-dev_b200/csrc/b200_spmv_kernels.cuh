@@ -66,6 +66,10 @@ struct SpmvSmem {
   static constexpr size_t BYTES = (size_t)STAGES * STAGE_ELEMS * 12 + STAGES * 8 + 64;
 };
 
+/* experiment switch (B200_SPMV_GATHER_CG, read once in b200_spmv.cu): the parked gather pass of irregular matrices loads x
+ * with ld.global.cg (L2 only) instead of ld.global.nc — its L1 hit rate is 2-3 %, so L1 allocation buys nothing */
+static __constant__ int b200_c_gather_cg;
+
 /* tiles[t] = {row_begin, row_end, k_begin, k_end} in visiting order (ci = offsets in visiting order; rindex maps a
  * visiting position to the row id when the block is stored compressed, else NULL). */
 template <int G, bool PARK, bool ADD, bool DOT, int THREADS, int TILE_NNZ, int STAGES>
@@ -173,8 +177,13 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
       } else {
         if (PARK) {
           /* balanced gather pass: products parked in place of the values, then the row sums read shared memory only */
+          if (b200_c_gather_cg) {
 #pragma unroll 8
-          for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldg(&x[sj[k]]);
+            for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldcg(&x[sj[k]]);
+          } else {
+#pragma unroll 8
+            for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldg(&x[sj[k]]);
+          }
           __syncthreads();
         }
         if (G == 1) {
