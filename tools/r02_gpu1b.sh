@@ -23,3 +23,4 @@ import sys,json
 for l in sys.stdin:
     if l.startswith('{'):
         d=json.loads(l); print('C2 upload %.3f s matmult %.4f ms cg %.4f ms'%(d['upload_s'], d['matmult_ms'], d['kspcg_fused']['ms_per_iter']))"
+for c in 8 7 6 5; do B200_SPMV_CTAS=$c python tools/spmv_bench.py lap7 2>&1 | grep "^lap7" | sed "s/^/ctas_per_sm=$c /"; done
