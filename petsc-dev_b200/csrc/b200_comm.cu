@@ -590,8 +590,7 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
 /* ------------------------------------------------------------------------------------------------ one-launch MatMult */
 struct FusedPlan {
   int    ntiles, grid, nboundary, threads, tile_nnz;
-  int4  *d_tiles;
-  int   *d_flag;
+  int   *d_bt_start, *d_bt_list;     /* boundary tiles of every CTA's walk (phase 2 of the kernel)                    */
   double *d_dotpart;
   unsigned *d_ticket_dot;
 };
@@ -600,7 +599,7 @@ void b200_mpiaij_fused_free(b200_mat M)
 {
   FusedPlan *fp = (FusedPlan *)M->fusedplan;
   if (!fp) return;
-  cudaFree(fp->d_tiles); cudaFree(fp->d_flag); cudaFree(fp->d_dotpart); cudaFree(fp->d_ticket_dot);
+  cudaFree(fp->d_bt_start); cudaFree(fp->d_bt_list); cudaFree(fp->d_dotpart); cudaFree(fp->d_ticket_dot);
   free(fp);
   M->fusedplan = NULL;
 }
@@ -642,37 +641,12 @@ static int fusedplan_build(b200_mat M, const int *Bi)
   if (A->nlong || A->compressed || A->nstrips > 1 || B->nstrips > 1 || A->cfg != 0 || A->park) return 0;
   if (A->m != A->n) return 0;
   if (B->nz * 4 > A->nz) return 0;                         /* a fat off-diagonal block streams better through its own TMA pipeline */
-  std::vector<int4> tiles((size_t)A->ntiles), sorted, inner, edge;
-  std::vector<int>  flag;
+  std::vector<int4> tiles((size_t)A->ntiles);
   B200_CUDA(cudaMemcpy(tiles.data(), A->d_tiles, sizeof(int4) * (size_t)A->ntiles, cudaMemcpyDeviceToHost));
+  int nb = 0;
   for (size_t t = 0; t < tiles.size(); t++) {
     if (tiles[t].y < 0) return 0;                          /* chunk of a long row: not on this path */
-    int4 d = tiles[t];
-    if (Bi[d.y] > Bi[d.x]) { d.z |= (int)0x80000000; edge.push_back(d); } else inner.push_back(d);
-  }
-  /* Visiting order.  Boundary tiles need the ghost values (a few microseconds of NVLink flight after the kernel starts)
-   * and cost a chain of dependent loads each (row offsets of B, its entries, the ghost values).  All of them at the END
-   * of the walk put that latency into the kernel's tail, where nothing is left to hide it (measured: +8 us on a 250 us
-   * product).  So: a lead of interior tiles (a quarter of them — the ghosts have landed long before it is through), then
-   * the boundary tiles spread evenly through the interior ones, then a tail of interior tiles only.  Any order gives the
-   * same y: a row's sum never leaves its lane. */
-  const int nb = (int)edge.size();
-  {
-    const size_t ni = inner.size();
-    size_t lead = ni / 4, tail = ni / 8;
-    const char *eo = getenv("B200_MPI_FUSED_ORDER");       /* 0: interior first, boundary last (the old order) */
-    if (eo && !atoi(eo)) { lead = ni; tail = 0; }
-    const size_t mid = ni - lead - tail;
-    sorted.reserve(tiles.size());
-    for (size_t t = 0; t < lead; t++) sorted.push_back(inner[t]);
-    size_t ie = 0;
-    for (size_t t = 0; t < mid; t++) {                      /* boundary tile e goes in after interior tile floor((e+1) mid / (nb+1)) */
-      while (ie < (size_t)nb && (ie + 1) * mid / ((size_t)nb + 1) <= t) sorted.push_back(edge[ie++]);
-      sorted.push_back(inner[lead + t]);
-    }
-    while (ie < (size_t)nb) sorted.push_back(edge[ie++]);
-    for (size_t t = lead + mid; t < ni; t++) sorted.push_back(inner[t]);
-    for (size_t t = 0; t < sorted.size(); t++) flag.push_back(sorted[t].z < 0 ? 1 : 0);
+    nb += Bi[tiles[t].y] > Bi[tiles[t].x];
   }
   FusedPlan *fp = (FusedPlan *)calloc(1, sizeof(FusedPlan));
   if (!fp) return b200_seterr(B200_ERR_MEM, "out of host memory");
@@ -690,10 +664,20 @@ static int fusedplan_build(b200_mat M, const int *Bi)
   /* every CTA of the grid is resident at once (waits on arrival flags never hold up a CTA that still has to send) */
   fp->grid = g_b200.nsm * occ;
   if (fp->grid > fp->ntiles) fp->grid = fp->ntiles;
-  B200_CUDA(cudaMalloc((void **)&fp->d_tiles, sizeof(int4) * sorted.size()));
-  B200_CUDA(cudaMemcpy(fp->d_tiles, sorted.data(), sizeof(int4) * sorted.size(), cudaMemcpyHostToDevice));
-  B200_CUDA(cudaMalloc((void **)&fp->d_flag, sizeof(int) * flag.size()));
-  B200_CUDA(cudaMemcpy(fp->d_flag, flag.data(), sizeof(int) * flag.size(), cudaMemcpyHostToDevice));
+  /* which tiles of each CTA's walk (t = c, c + grid, ...) hold rows with off-diagonal entries: phase 2 of the kernel */
+  {
+    std::vector<int> start((size_t)fp->grid + 1, 0), list;
+    list.reserve((size_t)nb);
+    for (int c = 0; c < fp->grid; c++) {
+      for (int t = c; t < A->ntiles; t += fp->grid)
+        if (Bi[tiles[t].y] > Bi[tiles[t].x]) list.push_back(t);
+      start[(size_t)c + 1] = (int)list.size();
+    }
+    B200_CUDA(cudaMalloc((void **)&fp->d_bt_start, sizeof(int) * start.size()));
+    B200_CUDA(cudaMemcpy(fp->d_bt_start, start.data(), sizeof(int) * start.size(), cudaMemcpyHostToDevice));
+    B200_CUDA(cudaMalloc((void **)&fp->d_bt_list, sizeof(int) * (list.size() + 1)));
+    if (!list.empty()) B200_CUDA(cudaMemcpy(fp->d_bt_list, list.data(), sizeof(int) * list.size(), cudaMemcpyHostToDevice));
+  }
   B200_CUDA(cudaMalloc((void **)&fp->d_dotpart, sizeof(double) * (size_t)(fp->grid + 1)));
   B200_CUDA(cudaMalloc((void **)&fp->d_ticket_dot, sizeof(unsigned)));
   B200_CUDA(cudaMemset(fp->d_ticket_dot, 0, sizeof(unsigned)));
@@ -723,7 +707,7 @@ int b200_mpiaij_mult_fused_cg(b200_mat M, const double *x, const double *yin, do
   M->epoch++;
   MpiSpmvArgs a;
   memset(&a, 0, sizeof(a));
-  a.ntiles = fp->ntiles; a.tiles = fp->d_tiles;
+  a.ntiles = fp->ntiles; a.tiles = M->A.d_tiles; a.bt_start = fp->d_bt_start; a.bt_list = fp->d_bt_list;
   a.ai = M->A.d_i; a.aj = M->A.d_j; a.aa = M->A.d_a;
   a.bi = M->B.d_i; a.bj = M->B.d_j; a.ba = M->B.d_a;
   a.x = x; a.yin = yin; a.z = z;

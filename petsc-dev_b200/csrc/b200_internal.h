@@ -118,7 +118,8 @@ struct b200_mat_s {
 };
 
 int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
-int  b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_j, double *d_a);
+int  b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_i, int *d_j, double *d_a);
+void *b200_pinned_scratch(size_t bytes);   /* one growing pinned host buffer for short-lived read-backs (single host thread per rank) */
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
 int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);

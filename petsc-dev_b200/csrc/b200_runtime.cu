@@ -245,7 +245,7 @@ extern "C" int b200_memset(void *dst, int byte, size_t bytes)
 /* ------------------------------------------------------------------------------------------------ staged uploads
  * Host -> device copy of a large PAGEABLE array (the CSR arrays a caller hands to b200_mat_create_*: the reference's
  * a->i/a->j/a->a come from PetscMalloc).  A plain cudaMemcpy stages such memory through one small driver buffer on one
- * thread (measured 7.5 GB/s for the 1.4 GB of configs[1]); here W host threads copy alternating 8 MB chunks into their
+ * thread (measured 7.5 GB/s for the 1.4 GB of configs[1]); here W host threads copy alternating 1 MB chunks into their
  * own pinned buffers and queue the DMA of each chunk on their own stream, so the host-side copies run in parallel and
  * overlap the transfers (what MatCUSPCopyToGPU's `assign` from a host array cannot do, aijcusp.cu:126-253).
  * Synchronous like the cudaMemcpy it replaces. */
@@ -253,14 +253,14 @@ extern "C" int b200_memset(void *dst, int byte, size_t bytes)
 #include <vector>
 #include <atomic>
 
-#define B200_UP_CHUNK   ((size_t)4 << 20)
+#define B200_UP_CHUNK   ((size_t)1 << 20)     /* pinning costs ~1 ms per MB: 16 MB in all for 8 workers */
 #define B200_UP_MAXW    8
 #define B200_UP_MIN     ((size_t)64 << 20)     /* below this one ordinary copy is as fast as setting the pipeline up */
 struct UpWorker { cudaStream_t st; void *buf[2]; cudaEvent_t ev[2]; bool ready; };
 static UpWorker g_up[B200_UP_MAXW];
 static int      g_up_max = 0;
 
-/* workers are set up one by one as uploads need them (pinning host memory is slow: ~8 MB per worker, a few ms each) */
+/* workers are set up one by one as uploads need them (pinning host memory is slow: 2 MB per worker, ~2 ms each) */
 static int up_worker_init(int k)
 {
   if (g_up[k].ready) return 0;
@@ -286,8 +286,23 @@ static int up_workers_for(size_t bytes)
   return w > (size_t)g_up_max ? g_up_max : (int)w;
 }
 
+static void  *g_pin_scratch = NULL;
+static size_t g_pin_scratch_bytes = 0;
+void *b200_pinned_scratch(size_t bytes)
+{
+  if (bytes > g_pin_scratch_bytes) {
+    if (g_pin_scratch) cudaFreeHost(g_pin_scratch);
+    g_pin_scratch = NULL; g_pin_scratch_bytes = 0;
+    const size_t want = bytes + (bytes >> 2) + 4096;
+    if (cudaHostAlloc(&g_pin_scratch, want, cudaHostAllocDefault) != cudaSuccess) { cudaGetLastError(); g_pin_scratch = NULL; return NULL; }
+    g_pin_scratch_bytes = want;
+  }
+  return g_pin_scratch;
+}
+
 void b200_upload_release(void)
 {
+  if (g_pin_scratch) { cudaFreeHost(g_pin_scratch); g_pin_scratch = NULL; g_pin_scratch_bytes = 0; }
   for (int k = 0; k < B200_UP_MAXW; k++) {
     if (!g_up[k].ready) continue;
     cudaStreamDestroy(g_up[k].st);

@@ -108,20 +108,21 @@ void b200_seq_free(B200Seq *S)
 }
 
 /* i is a host array.  j / a are host arrays that are copied, unless adopt: then they are device arrays of nz + 8
- * entries (cudaMalloc'ed by the caller, e.g. the device assembly) whose ownership passes to S. */
-static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a, bool adopt = false)
+ * entries (cudaMalloc'ed by the caller, e.g. the device assembly) whose ownership passes to S, and d_i_adopt — the
+ * device copy of i the caller already has, m + 1 entries — is adopted as well instead of being uploaded again. */
+static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a, bool adopt = false, int *d_i_adopt = NULL)
 {
   memset(S, 0, sizeof(*S));
   {
     static bool gather_mode_set = false;
     if (!gather_mode_set) {
       const char *e = getenv("B200_SPMV_GATHER_CG");
-      const int v = e ? atoi(e) : 0;
+      const int v = e ? atoi(e) : 1;
       B200_CUDA(cudaMemcpyToSymbol(b200_c_gather_cg, &v, sizeof(int)));
       gather_mode_set = true;
     }
   }
-  if (adopt) { S->d_j = const_cast<int *>(j); S->d_a = const_cast<double *>(a); }   /* owned from here on, also on failure */
+  if (adopt) { S->d_j = const_cast<int *>(j); S->d_a = const_cast<double *>(a); S->d_i = d_i_adopt; }   /* owned from here on, also on failure */
   if (m < 0 || n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative matrix size %d x %d", m, n);
   if (!i || i[0] != 0) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets must start at 0");
   const long long nz = i[m];
@@ -237,8 +238,10 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   if (S->grid > S->ntiles) S->grid = S->ntiles;
 
   const size_t pad = 8;
-  B200_CUDA(cudaMalloc((void **)&S->d_i, sizeof(int) * ((size_t)m + 1)));
-  B200_CHK(b200_upload_pageable(S->d_i, i, sizeof(int) * ((size_t)m + 1)));
+  if (!S->d_i) {
+    B200_CUDA(cudaMalloc((void **)&S->d_i, sizeof(int) * ((size_t)m + 1)));
+    B200_CHK(b200_upload_pageable(S->d_i, i, sizeof(int) * ((size_t)m + 1)));
+  }
   if (!adopt) {
     B200_CUDA(cudaMalloc((void **)&S->d_j, sizeof(int) * ((size_t)nz + pad)));
     B200_CUDA(cudaMalloc((void **)&S->d_a, sizeof(double) * ((size_t)nz + pad)));
@@ -352,11 +355,11 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
 }
 
 /* Block from a CSR whose column ids and values already live on the device (device assembly, b200_assembly.cu): only
- * the row offsets pass through the host (the row binning is computed from them); d_j / d_a (nz + 8 entries each) are
- * adopted.  Column strips are not formed on this path. */
-int b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_j, double *d_a)
+ * the row offsets pass through the host (the row binning is computed from them); d_i (m + 1 entries, may be NULL: then
+ * i_host is uploaded) and d_j / d_a (nz + 8 entries each) are adopted.  Column strips are not formed on this path. */
+int b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_i, int *d_j, double *d_a)
 {
-  return seq_upload_one(S, m, n, i_host, d_j, d_a, true);
+  return seq_upload_one(S, m, n, i_host, d_j, d_a, true, d_i);
 }
 
 extern "C" int b200_spmv_set_strips(int nstrips)

@@ -66,14 +66,18 @@ struct SpmvSmem {
   static constexpr size_t BYTES = (size_t)STAGES * STAGE_ELEMS * 12 + STAGES * 8 + 64;
 };
 
-/* experiment switch (B200_SPMV_GATHER_CG, read once in b200_spmv.cu): the parked gather pass of irregular matrices loads x
- * with ld.global.cg (L2 only) instead of ld.global.nc — its L1 hit rate is 2-3 %, so L1 allocation buys nothing */
+/* The parked gather pass of irregular matrices loads x with ld.global.cg (L2 only): its L1 hit rate is 2-3 % (ncu,
+ * profiles/r02_spmv_plaw_10M_full.txt), so allocating the lines in L1 only costs tag work — measured 0.744 ms against
+ * 0.799 ms with ld.global.nc on the 2 M-row power-law sample.  B200_SPMV_GATHER_CG=0 (read once in b200_spmv.cu) restores
+ * the ld.global.nc loads for comparison. */
 static __constant__ int b200_c_gather_cg;
 
 /* tiles[t] = {row_begin, row_end, k_begin, k_end} in visiting order (ci = offsets in visiting order; rindex maps a
  * visiting position to the row id when the block is stored compressed, else NULL). */
+/* the default shape (256 lanes, one stage) is held to 32 registers = 8 resident CTAs per SM in every variant: at 40
+ * registers (6 CTAs) the same walk streams 5 % slower (0.262 ms against 0.250 ms per 256^3 product) */
 template <int G, bool PARK, bool ADD, bool DOT, int THREADS, int TILE_NNZ, int STAGES>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, (THREADS == 256 && STAGES == 1) ? ((ADD && DOT) ? 6 : 8) : 1)   /* ADD+DOT would spill at 32 */
 spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
                  const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
                  const double *yin, double *z, double *__restrict__ dotpart, double *__restrict__ longpart,
@@ -91,14 +95,12 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
   const int tid = threadIdx.x, r = tid / G, g = tid % G;
   const int stride = gridDim.x;
   int t = blockIdx.x;
-  uint64_t pol = 0;
 
   if (tid == 0) {
 #pragma unroll
     for (int s = 0; s < STAGES; s++) b200_mbar_init(&bars[s], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    pol = b200_policy_evict_first();
   }
   __syncthreads();
 
@@ -106,6 +108,7 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
     const int ka = d.z & ~3, kb = (d.w + 3) & ~3;
     const uint32_t n = (uint32_t)(kb - ka);
     if (n == 0) { b200_mbar_expect_tx(&bars[s], 0); return; }
+    const uint64_t pol = b200_policy_evict_first();  /* made where it is used: two registers less across the tile loop */
     b200_mbar_expect_tx(&bars[s], n * 12u);
     b200_bulk_g2s(s_a + (size_t)s * SE, aa + ka, n * 8u, &bars[s], pol);
     b200_bulk_g2s(s_j + (size_t)s * SE, aj + ka, n * 4u, &bars[s], pol);
@@ -126,11 +129,13 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
   if (t + stride < ntiles) d_nxt = __ldg(&tiles[t + stride]);
   int b_cur = 0, e_cur = 0, row_cur = -1;
   double y_cur = 0.0;
+  /* b, e are positions INSIDE the tile's stage (entry number minus the tile's aligned first entry): the row sums index
+     the stage directly, no per-tile base pointers live in registers (this is what lets the ADD variants fit 32 registers) */
   auto load_row = [&](const int4 &d, int &b, int &e, int &row, double &y0) {
     row = -1; b = e = 0;
     if (r < d.y - d.x) {
-      const int p = d.x + r;
-      b = __ldg(&ci[p]); e = __ldg(&ci[p + 1]);
+      const int p = d.x + r, ka = d.z & ~3;
+      b = __ldg(&ci[p]) - ka; e = __ldg(&ci[p + 1]) - ka;
       row = rindex ? __ldg(&rindex[p]) : p;
       if (ADD && g == 0) y0 = yin[row];
     }
@@ -150,18 +155,18 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
 
     b200_mbar_wait(&bars[s], parity);
     {
-      const int ka = d_cur.z & ~3;
-      double    *sa = s_a + (size_t)s * SE - ka;             /* indexed by the global entry number */
-      const int *sj = s_j + (size_t)s * SE - ka;
+      double    *sa = s_a + (size_t)s * SE;                  /* indexed by the position inside the stage */
+      const int *sj = s_j + (size_t)s * SE;
+      const int k0 = d_cur.z - (d_cur.z & ~3), k1 = d_cur.w - (d_cur.z & ~3);   /* the tile's entries inside the stage */
       if (d_cur.y < 0) {
         /* one chunk of a long row: every lane strides the chunk, fixed-shape block tree, partial -> longpart[slot] */
         double p0 = 0.0, p1 = 0.0;
-        int k = d_cur.z + tid;
-        for (; k + THREADS < d_cur.w; k += 2 * THREADS) {
+        int k = k0 + tid;
+        for (; k + THREADS < k1; k += 2 * THREADS) {
           p0 += sa[k] * __ldg(&x[sj[k]]);
           p1 += sa[k + THREADS] * __ldg(&x[sj[k + THREADS]]);
         }
-        if (k < d_cur.w) p0 += sa[k] * __ldg(&x[sj[k]]);
+        if (k < k1) p0 += sa[k] * __ldg(&x[sj[k]]);
         double v = p0 + p1;
         const int lane = tid & 31, wid = tid >> 5;
 #pragma unroll
@@ -179,10 +184,10 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
           /* balanced gather pass: products parked in place of the values, then the row sums read shared memory only */
           if (b200_c_gather_cg) {
 #pragma unroll 8
-            for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldcg(&x[sj[k]]);
+            for (int k = k0 + tid; k < k1; k += THREADS) sa[k] = sa[k] * __ldcg(&x[sj[k]]);
           } else {
 #pragma unroll 8
-            for (int k = d_cur.z + tid; k < d_cur.w; k += THREADS) sa[k] = sa[k] * __ldg(&x[sj[k]]);
+            for (int k = k0 + tid; k < k1; k += THREADS) sa[k] = sa[k] * __ldg(&x[sj[k]]);
           }
           __syncthreads();
         }

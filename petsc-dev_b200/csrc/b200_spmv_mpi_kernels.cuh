@@ -7,13 +7,13 @@
  *            (Pack_1 + send + UnPack_1 fused, as pack_put_kernel does stand-alone), one system-scope fence per CTA, and the
  *            last of them raises the arrival flag on every neighbour.  Nothing in phase 0 waits on the current exchange of
  *            any rank (only on credits of exchanges two steps back), so no cycle of waits can form between ranks;
- *   tiles    interior tiles first.  Tiles holding rows with off-diagonal entries ("boundary tiles") come last: the first
- *            time a CTA reaches one it waits (ld.acquire.sys) for the arrival flags of this exchange — by then the ghost
- *            values have normally landed long ago — and each row's lane CONTINUES its register sum over the row's
- *            off-diagonal entries (ghost values read with ld.global.cg, they were written by another GPU).  That is the
- *            association of MatMultAdd_SeqAIJ started from y_i (aij.c:1338): with one lane per row the result is
- *            bit-identical to the reference's two-step product, and y is written once instead of written, re-read and
- *            re-written.
+ *   tiles    the sequential kernel's walk over the diagonal block, unchanged (same registers, same 8 CTAs per SM);
+ *   phase 2  the CTA then waits (ld.acquire.sys) for the arrival flags of this exchange — the ghost values landed while
+ *            the tiles streamed — and revisits those of ITS tiles that hold rows with off-diagonal entries: each such
+ *            row's lane re-reads the z it wrote and CONTINUES the sum over the row's off-diagonal entries (ghost values
+ *            read with ld.global.cg, they were written by another GPU).  That is the association of MatMultAdd_SeqAIJ
+ *            started from y_i (aij.c:1338): with one lane per row the result is bit-identical to the reference's
+ *            two-step product.  Only the boundary rows (under 1 % for a slab of a 3-D grid) are touched twice.
  * No second launch, no event join, no wait kernel.  Used when the off-diagonal block is thin (stencil-like operators);
  * matrices whose off-diagonal block carries most of the entries keep the two-product path of b200_comm.cu. */
 #ifndef B200_SPMV_MPI_KERNELS_CUH
@@ -24,8 +24,9 @@
 
 struct MpiSpmvArgs {
   int           ntiles;
-  const int4   *tiles;        /* {row_begin, row_end, k_begin, k_end} of the diagonal block, interior tiles first; the sign
-                                 bit of k_begin marks a tile with off-diagonal entries in some row ("boundary tile")     */
+  const int4   *tiles;        /* {row_begin, row_end, k_begin, k_end} of the diagonal block (the sequential kernel's table)    */
+  const int    *bt_start, *bt_list;   /* per CTA of the launch grid: which tiles of its walk hold rows with off-diagonal
+                                         entries ("boundary tiles"), bt_list[bt_start[c] .. bt_start[c+1])                */
   const int    *ai, *aj;  const double *aa;       /* diagonal block                                                     */
   const int    *bi, *bj;  const double *ba;       /* off-diagonal block, full row offsets [m+1], columns index lvec     */
   const double *x, *yin;  double *z;
@@ -45,22 +46,11 @@ struct MpiSpmvArgs {
   unsigned     *ticket_dot;
 };
 
-/* The off-diagonal entries of one row, lane g of G striding them, added to `sum` in order (kept out of line: it runs for
- * the boundary tiles only and must not cost the streaming loop registers). */
-template <int G>
-__device__ __noinline__ double b200_offdiag_row(const int *__restrict__ bi, const int *__restrict__ bj, const double *__restrict__ ba,
-                                                const double *lvec, int row, int g, double sum)
-{
-  const int bb = __ldg(&bi[row]), be = __ldg(&bi[row + 1]);
-  for (int k = bb + g; k < be; k += G) sum += __ldg(&ba[k]) * __ldcg(&lvec[__ldg(&bj[k])]);   /* aij.c:1338, continued */
-  return sum;
-}
-
-/* 6 resident CTAs per SM = the 40 registers the kernel wants.  Holding it to the sequential kernel's 8 CTAs (32 registers)
- * spills ~50 bytes inside the tile loop and was measured 1.7x SLOWER on 2 GPUs (0.441 ms against 0.258 ms per 256^3
- * product, profiles/r02_bench_n2_*.json), so that variant is gone. */
+#ifndef FUSED_CTAS_PER_SM
+#define FUSED_CTAS_PER_SM 8        /* 32 registers, like the sequential kernel: 2048 resident lanes per SM */
+#endif
 template <int G, bool ADD, bool DOT, int THREADS, int TILE_NNZ>
-__global__ void __launch_bounds__(THREADS, 6)
+__global__ void __launch_bounds__(THREADS, FUSED_CTAS_PER_SM)
 spmv_mpiaij_kernel(const MpiSpmvArgs a)
 {
   constexpr int SE = TILE_NNZ + SPMV_ALIGN_PAD;
@@ -77,20 +67,19 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
   const int stride = gridDim.x;
   const int ntiles = a.ntiles;
   int t = blockIdx.x;
-  uint64_t pol = 0;
 
   if (tid == 0) {
     b200_mbar_init(&bars[0], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    pol = b200_policy_evict_first();
   }
   __syncthreads();
 
   auto issue = [&](int4 d) {                        /* thread 0 only */
-    const int ka = (d.z & 0x7fffffff) & ~3, kb = (d.w + 3) & ~3;
+    const int ka = d.z & ~3, kb = (d.w + 3) & ~3;
     const uint32_t n = (uint32_t)(kb - ka);
     if (n == 0) { b200_mbar_expect_tx(&bars[0], 0); return; }
+    const uint64_t pol = b200_policy_evict_first();  /* made where it is used: two registers less across the tile loop */
     b200_mbar_expect_tx(&bars[0], n * 12u);
     b200_bulk_g2s(s_a, a.aa + ka, n * 8u, &bars[0], pol);
     b200_bulk_g2s(s_j, a.aj + ka, n * 4u, &bars[0], pol);
@@ -126,22 +115,23 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
   }
 
   /* ---- tiles ---- */
-  int4 d_cur = make_int4(0, 0, 0, 0), d_nxt = make_int4(0, 0, 0, 0);
-  if (t < ntiles) d_cur = __ldg(&a.tiles[t]);
+  int4 d_nxt = make_int4(0, 0, 0, 0);
   if (t + stride < ntiles) d_nxt = __ldg(&a.tiles[t + stride]);
   int b_cur = 0, e_cur = 0, row_cur = -1;
   double y_cur = 0.0;
+  /* b, e are positions INSIDE the tile's stage (entry number minus the tile's aligned first entry), so the sums below
+     index the two shared arrays directly: no per-tile base pointers to keep in registers */
   auto load_row = [&](const int4 &d, int &b, int &e, int &row, double &y0) {
     row = -1; b = e = 0;
     if (r < d.y - d.x) {
       row = d.x + r;
-      b = __ldg(&a.ai[row]); e = __ldg(&a.ai[row + 1]);
+      const int ka = d.z & ~3;
+      b = __ldg(&a.ai[row]) - ka; e = __ldg(&a.ai[row + 1]) - ka;
       if (ADD && g == 0) y0 = a.yin[row];
     }
   };
-  if (t < ntiles) load_row(d_cur, b_cur, e_cur, row_cur, y_cur);
+  if (t < ntiles) load_row(__ldg(&a.tiles[t]), b_cur, e_cur, row_cur, y_cur);
 
-  bool arrived = false;
   double dot = 0.0;
   for (int it = 0; t < ntiles; it++, t += stride) {
     const uint32_t parity = (uint32_t)(it & 1);
@@ -150,46 +140,31 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
     int4 d_nn = make_int4(0, 0, 0, 0);
     if (t + stride < ntiles) load_row(d_nxt, b_nxt, e_nxt, row_nxt, y_nxt);
     if (t + 2 * stride < ntiles) d_nn = __ldg(&a.tiles[t + 2 * stride]);
-    const bool f_cur = d_cur.z < 0;
 
-    if (f_cur && !arrived) {
-      /* VecScatterEnd: the ghost values of this exchange are in lvec once every sender's flag shows the epoch */
-      if (tid < a.plan.nfrom) { const long long t0 = clock64(); while (ld_acquire_sys(a.plan.lflag[tid]) < a.epoch) b200_spin_guard(t0); }
-      __syncthreads();
-      arrived = true;
-    }
     b200_mbar_wait(&bars[0], parity);
-    {
-      const int ka = (d_cur.z & 0x7fffffff) & ~3;
-      const double *sa = s_a - ka;                   /* indexed by the global entry number */
-      const int    *sj = s_j - ka;
-      if (G == 1) {
-        if (row_cur >= 0) {
-          double sum = ADD ? y_cur : 0.0;
+    if (G == 1) {
+      if (row_cur >= 0) {
+        double sum = ADD ? y_cur : 0.0;
 #pragma unroll 4
-          for (int k = b_cur; k < e_cur; k++) sum += sa[k] * __ldg(&a.x[sj[k]]);
-          if (f_cur) sum = b200_offdiag_row<1>(a.bi, a.bj, a.ba, a.lvec, row_cur, 0, sum);   /* boundary tiles only */
-          a.z[row_cur] = sum;
-          if (DOT) {
-            const double xd = __ldg(&a.dotx[row_cur]);
-            dot += xd * sum;
-            if (ADD) dot -= xd * y_cur;
-          }
+        for (int k = b_cur; k < e_cur; k++) sum += s_a[k] * __ldg(&a.x[s_j[k]]);
+        a.z[row_cur] = sum;
+        if (DOT) {
+          const double xd = __ldg(&a.dotx[row_cur]);
+          dot += xd * sum;
+          if (ADD) dot -= xd * y_cur;
         }
-      } else {
-        double sum = 0.0, sb = 0.0;
+      }
+    } else {
+      double sum = 0.0;
 #pragma unroll 4
-        for (int k = b_cur + g; k < e_cur; k += G) sum += sa[k] * __ldg(&a.x[sj[k]]);
-        if (f_cur && row_cur >= 0) sb = b200_offdiag_row<G>(a.bi, a.bj, a.ba, a.lvec, row_cur, g, 0.0);
-        __syncwarp();
+      for (int k = b_cur + g; k < e_cur; k += G) sum += s_a[k] * __ldg(&a.x[s_j[k]]);
+      __syncwarp();
 #pragma unroll
-        for (int o = G / 2; o > 0; o >>= 1) { sum += __shfl_xor_sync(0xffffffffu, sum, o, G); sb += __shfl_xor_sync(0xffffffffu, sb, o, G); }
-        if (g == 0 && row_cur >= 0) {
-          if (ADD) sum = y_cur + sum;
-          sum = sum + sb;                             /* diagonal block first, then the off-diagonal block */
-          if (DOT) { const double xd = __ldg(&a.dotx[row_cur]); dot += xd * sum; if (ADD) dot -= xd * y_cur; }
-          a.z[row_cur] = sum;
-        }
+      for (int o = G / 2; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o, G);
+      if (g == 0 && row_cur >= 0) {
+        if (ADD) sum = y_cur + sum;
+        if (DOT) { const double xd = __ldg(&a.dotx[row_cur]); dot += xd * sum; if (ADD) dot -= xd * y_cur; }
+        a.z[row_cur] = sum;
       }
     }
     __syncthreads();                                  /* everyone is done with the stage */
@@ -197,8 +172,49 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
       const int tt = t + stride;
       if (tt < ntiles) issue(d_nxt);
     }
-    d_cur = d_nxt; d_nxt = d_nn;
+    d_nxt = d_nn;
     b_cur = b_nxt; e_cur = e_nxt; row_cur = row_nxt; y_cur = y_nxt;
+  }
+
+  /* ---- VecScatterEnd + y += B lvec on the rows that have off-diagonal entries ----
+   * bt_list[bt_start[c] .. bt_start[c+1]) are the tiles of THIS CTA's walk that hold such rows (built with the plan for
+   * exactly this grid), so every row is finished by the thread that wrote its diagonal part above: z[row] is re-read and
+   * the row's lane CONTINUES the sum over the off-diagonal entries — the association of MatMultAdd_SeqAIJ started from
+   * y_i (aij.c:1338), bit-identical to the reference's two-step product with one lane per row.  Kept out of the tile loop:
+   * in it, the call cost the loop 8 registers, i.e. two of the eight resident CTAs per SM (0.262 ms against 0.250 ms per
+   * 256^3 product, profiles/r02_ctas_per_sm.txt). */
+  {
+    const int q0 = __ldg(&a.bt_start[blockIdx.x]), q1 = __ldg(&a.bt_start[blockIdx.x + 1]);
+    if (q1 > q0) {
+      /* the ghost values of this exchange are in lvec once every sender's flag shows the epoch */
+      if (tid < a.plan.nfrom) { const long long t0 = clock64(); while (ld_acquire_sys(a.plan.lflag[tid]) < a.epoch) b200_spin_guard(t0); }
+      __syncthreads();
+    }
+    for (int q = q0; q < q1; q++) {
+      const int4 d = __ldg(&a.tiles[__ldg(&a.bt_list[q])]);
+      int bb = 0, be = 0, row = -1;
+      if (r < d.y - d.x) { row = d.x + r; bb = __ldg(&a.bi[row]); be = __ldg(&a.bi[row + 1]); }
+      if (G == 1) {
+        if (be > bb) {
+          const double z0 = a.z[row];
+          double sum = z0;
+          for (int k = bb; k < be; k++) sum += __ldg(&a.ba[k]) * __ldcg(&a.lvec[__ldg(&a.bj[k])]);   /* ghost values: written by another GPU */
+          a.z[row] = sum;
+          if (DOT) { const double xd = __ldg(&a.dotx[row]); dot += xd * sum; dot -= xd * z0; }
+        }
+      } else {
+        double sb = 0.0;
+        for (int k = bb + g; k < be; k += G) sb += __ldg(&a.ba[k]) * __ldcg(&a.lvec[__ldg(&a.bj[k])]);
+        __syncwarp();
+#pragma unroll
+        for (int o = G / 2; o > 0; o >>= 1) sb += __shfl_xor_sync(0xffffffffu, sb, o, G);
+        if (g == 0 && be > bb) {
+          const double z0 = a.z[row], sum = z0 + sb;   /* diagonal block first, then the off-diagonal block */
+          a.z[row] = sum;
+          if (DOT) { const double xd = __ldg(&a.dotx[row]); dot += xd * sum; dot -= xd * z0; }
+        }
+      }
+    }
   }
 
   if (DOT) {
