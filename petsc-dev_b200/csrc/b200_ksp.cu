@@ -451,13 +451,31 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
    * early when the device-side convergence test fires, so the host need not look often */
   const bool persist = !multi && seq && b200_cg_persistent_ok(A);
   if (persist && check_every < 256) check_every = 256;
-  int launched = 0, rc = 0;
+  /* short iterations on one GPU: the host cannot launch four kernels as fast as the GPU finishes them (measured floor:
+   * 22 us per iteration however small the matrix).  A block of iterations is therefore captured ONCE as a CUDA graph
+   * (every kernel argument is the same from iteration to iteration: the scalars live in the CgState on the device) and
+   * replayed; the first block runs directly (it also triggers the kernels' one-time attribute calls). */
+  bool use_graph = !multi && seq && !persist && A->A.nz <= (64ll << 20) && A->A.nlong == 0;
+  { const char *eg = getenv("B200_CG_GRAPH"); if (eg) use_graph = use_graph && atoi(eg) != 0; }
+  if (use_graph && check_every < 64) check_every = 64;
+  cudaGraphExec_t gexec = NULL;
+  long long graph_launches = 0;
+  bool capturing = false;
+  int launched = 0, rc = 0, nbatch = 0;
   while (launched < max_it) {
     int batch = check_every;
     if (launched + batch > max_it) batch = max_it - launched;
+    const long long l0 = c.launches;
     if (persist) {
       rc = b200_cg_persistent_run(A, pc->type == 1, pc->d, X, R, Z, P, ds, dhist, batch); if (rc) goto done;
-    } else
+    } else if (gexec && batch == check_every) {
+      if (cudaGraphLaunch(gexec, st) != cudaSuccess) { rc = b200_cuda_err(cudaGetLastError(), "cudaGraphLaunch", __FILE__, __LINE__); goto done; }
+      c.launches += graph_launches;
+    } else {
+    if (use_graph && !gexec && nbatch >= 1 && batch == check_every) {
+      if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) capturing = true;
+      else { cudaGetLastError(); use_graph = false; }
+    }
     for (int k = 0; k < batch; k++) {
       cg_pupdate_kernel<<<gp, 256, 0, st>>>(n, ds, P, Z);
       B200_LAUNCHED(1);
@@ -518,6 +536,18 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
         B200_LAUNCHED(1);
       }
     }
+    if (capturing) {
+      cudaGraph_t g = NULL;
+      capturing = false;
+      if (cudaStreamEndCapture(st, &g) != cudaSuccess || !g) { rc = b200_cuda_err(cudaGetLastError(), "cudaStreamEndCapture", __FILE__, __LINE__); goto done; }
+      const cudaError_t ei = cudaGraphInstantiate(&gexec, g, 0);
+      cudaGraphDestroy(g);
+      if (ei != cudaSuccess) { gexec = NULL; rc = b200_cuda_err(ei, "cudaGraphInstantiate", __FILE__, __LINE__); goto done; }
+      graph_launches = c.launches - l0;                 /* the capture recorded this block; now it runs */
+      if (cudaGraphLaunch(gexec, st) != cudaSuccess) { rc = b200_cuda_err(cudaGetLastError(), "cudaGraphLaunch", __FILE__, __LINE__); goto done; }
+    }
+    }
+    nbatch++;
     launched += batch;
     if (cudaMemcpyAsync(ps, ds, sizeof(CgState), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
       rc = b200_cuda_err(cudaGetLastError(), "CG state readback", __FILE__, __LINE__); goto done;
@@ -534,6 +564,8 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
     hist->len = hist_off + ps->nhist;
   }
 done:
+  if (capturing) { cudaGraph_t g = NULL; cudaStreamEndCapture(st, &g); if (g) cudaGraphDestroy(g); cudaGetLastError(); }
+  if (gexec) cudaGraphExecDestroy(gexec);
   b200_free(ds); b200_host_free(ps); b200_free(dhist);
   return rc;
 }

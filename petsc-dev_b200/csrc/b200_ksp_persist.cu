@@ -1,9 +1,8 @@
 /* b200_ksp_persist.cu — KSPSolve_CG (src/ksp/ksp/impls/cg/cg.c:181-281) as ONE persistent cooperative kernel per block of
  * iterations, for problems whose iteration is shorter than the kernel boundaries around it.
  *
- * configs[0] (2-D 5-point Laplacian 1000^2: 80 MB of matrix, everything L2-resident) moves ~12 us of traffic per CG
- * iteration; the four launches per iteration of the multi-kernel driver (p-update, SpMV+dot, scalar step, update+dots)
- * cost ~47 us.  Here the grid stays resident for `iters` iterations and the phases are separated by grid barriers:
+ * An experiment kept as an option (B200_CG_PERSISTENT=1), not the default: see b200_cg_persistent_ok for the numbers.
+ * The grid stays resident for `iters` iterations and the phases are separated by grid barriers:
  *
  *   A  p = z + b p                                   | barrier
  *   B  w = A p (TMA-fed row tiles, one lane group per row, partial p.w per CTA)
@@ -307,12 +306,12 @@ bool b200_cg_persistent_ok(b200_mat A)
   int coop = 0;
   if (cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, g_b200.device) != cudaSuccess || !coop) return false;
   if (e && atoi(e)) return true;
-  /* automatic: problems whose iteration is short enough for the launch boundaries to matter.  Measured on configs[0]
-   * (1000^2 5-point, 5 M entries): 42.8 us per iteration persistent against 40.6 us with four launches — the three grid
-   * barriers and their serial sections cost what the launches cost; below ~1 M entries the barriers win */
-  long long lim = 1ll << 20;
-  { const char *el = getenv("B200_CG_PERSIST_MAXNZ"); if (el && atoll(el) > 0) lim = atoll(el); }
-  return S->nz <= lim;
+  /* Opt-in only (B200_CG_PERSISTENT=1).  Measured on ex2's 5-point Laplacian, m = n = 100 ... 1000 (profiles/
+   * r02_c1_sweep.txt): 23.6 / 24.0 / 27.3 / 42.0 us per iteration at 10^4 / 9 10^4 / 2.5 10^5 / 10^6 rows against 22.7 / 22.8 /
+   * 25.4 / 41.1 us with four launches — three grid-wide barriers with a serial scalar section each cost what the four
+   * launches cost, at every size.  What the small problems were short of was host launch rate, and the CUDA-graph replay
+   * of the four-launch iteration (b200_ksp.cu) fixes that without the barriers. */
+  return false;
 }
 
 static unsigned *g_bar = NULL;

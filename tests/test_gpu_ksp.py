@@ -210,3 +210,35 @@ def test_ex10_style_binary_file_solve(gpu, R, P, tmp_path):
     assert abs(its - rr["its"]) <= 1
     k = min(len(hist), len(rr["history"]))
     assert np.max(np.abs(hist[:k] - rr["history"][:k]) / rr["history"][:k]) < 1e-10
+
+
+@pytest.mark.parametrize("mode", ["graph", "launches", "persistent"])
+def test_fused_cg_block_replay_modes(gpu, R, P, mode, monkeypatch):
+    """Several hundred iterations on a small matrix, so that the fused CG driver gets past its first block of iterations:
+    from the second block on the iterations are a CUDA-graph replay (default for small single-GPU problems), plain
+    launches (B200_CG_GRAPH=0) or the persistent cooperative kernel (B200_CG_PERSISTENT=1) — same arithmetic, so the same
+    history as the reference's KSPSolve_CG within 1e-10 and the same iteration count in all three."""
+    if mode == "launches":
+        monkeypatch.setenv("B200_CG_GRAPH", "0")
+    if mode == "persistent":
+        monkeypatch.setenv("B200_CG_PERSISTENT", "1")
+    ip, j, a = P.laplace2d_5pt(70, 64)
+    n = 70 * 64
+    ref = R.RefMat(n, n, ip, j, a, no_inode=True)
+    bh = ref.mult(P.random_vector(n, 3))
+    rr = ref.ksp_solve(bh, "cg", "jacobi", rtol=1e-12, maxit=10000)
+    assert rr["its"] > 150, rr["its"]                   # at least three blocks of 64
+    A = gpu.Mat.from_csr(n, n, ip, j, a)
+    b, x = gpu.Vec(n, bh), gpu.Vec(n)
+    r = gpu.ksp_solve(A, b, x, ksp_type="cg", pc_type="jacobi", rtol=1e-12, fused=1)
+    assert r["its"] == rr["its"] and r["reason"] == rr["reason"], (r["its"], rr["its"], r["reason"], rr["reason"])
+    assert len(r["history"]) == len(rr["history"])
+    assert _hist_dev(r["history"], rr["history"], window=1e-7) <= 1e-10
+    assert np.linalg.norm(x.get_array() - rr["x"]) <= 1e-8 * np.linalg.norm(rr["x"])
+    # a second solve on the same operator (a fresh graph is captured per solve) with a different right-hand side
+    bh2 = ref.mult(P.random_vector(n, 4))
+    rr2 = ref.ksp_solve(bh2, "cg", "jacobi", rtol=1e-12, maxit=10000)
+    b.set_array(bh2)
+    r2 = gpu.ksp_solve(A, b, x, ksp_type="cg", pc_type="jacobi", rtol=1e-12, fused=1)
+    assert r2["its"] == rr2["its"]
+    assert _hist_dev(r2["history"], rr2["history"], window=1e-7) <= 1e-10
