@@ -457,22 +457,24 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
    * replayed; the first block runs directly (it also triggers the kernels' one-time attribute calls). */
   bool use_graph = !multi && seq && !persist && A->A.nz <= (64ll << 20) && A->A.nlong == 0;
   { const char *eg = getenv("B200_CG_GRAPH"); if (eg) use_graph = use_graph && atoi(eg) != 0; }
-  if (use_graph && check_every < 64) check_every = 64;
+  const int gblock = 64;                                    /* iterations per graph; the host looks every check_every */
+  if (use_graph) check_every = check_every < gblock ? gblock : (check_every / gblock) * gblock;
+  const int block = use_graph ? gblock : check_every;       /* iterations issued per pass of the loop below */
   cudaGraphExec_t gexec = NULL;
   long long graph_launches = 0;
   bool capturing = false;
-  int launched = 0, rc = 0, nbatch = 0;
+  int launched = 0, rc = 0, nbatch = 0, since_check = 0;
   while (launched < max_it) {
-    int batch = check_every;
+    int batch = block;
     if (launched + batch > max_it) batch = max_it - launched;
     const long long l0 = c.launches;
     if (persist) {
       rc = b200_cg_persistent_run(A, pc->type == 1, pc->d, X, R, Z, P, ds, dhist, batch); if (rc) goto done;
-    } else if (gexec && batch == check_every) {
+    } else if (gexec && batch == block) {
       if (cudaGraphLaunch(gexec, st) != cudaSuccess) { rc = b200_cuda_err(cudaGetLastError(), "cudaGraphLaunch", __FILE__, __LINE__); goto done; }
       c.launches += graph_launches;
     } else {
-    if (use_graph && !gexec && nbatch >= 1 && batch == check_every) {
+    if (use_graph && !gexec && nbatch >= 1 && batch == block) {
       if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) == cudaSuccess) capturing = true;
       else { cudaGetLastError(); use_graph = false; }
     }
@@ -549,6 +551,9 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
     }
     nbatch++;
     launched += batch;
+    since_check += batch;
+    if (since_check < check_every && launched < max_it) continue;
+    since_check = 0;
     if (cudaMemcpyAsync(ps, ds, sizeof(CgState), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess) {
       rc = b200_cuda_err(cudaGetLastError(), "CG state readback", __FILE__, __LINE__); goto done;
     }

@@ -14,18 +14,18 @@ for m in (100, 200, 300, 500, 700, 1000):
     one, b, sol = pb.Vec(n), pb.Vec(n), pb.Vec(n)
     one.set(1.0); A.mult(one, b)
     out = {}
-    for mode in ("1", "0"):
-        os.environ["B200_CG_PERSISTENT"] = mode
+    for mode, env in (("persistent", {"B200_CG_PERSISTENT": "1"}), ("launches", {"B200_CG_GRAPH": "0"}), ("graph", {})):
+        os.environ.update(env)
         pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=20, fused=1, histmax=0)
-        r = pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=400, fused=1, check_every=400, histmax=0)
+        r = pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=1280, fused=1, check_every=256, histmax=0)
         out[mode] = 1e3 * r["solve_ms"] / r["its"]
-    del os.environ["B200_CG_PERSISTENT"]
+        for k in env: del os.environ[k]
     x, y = pb.Vec(n, P.random_vector(n, 2)), pb.Vec(n)
     for _ in range(5): A.mult(x, y)
     pb.synchronize(); pb.timer_start()
     for _ in range(200): A.mult(x, y)
     mm = 1e3 * pb.timer_stop() / 200
-    print("m=%4d rows %7d nnz %8d  CG us/iter: persistent %.2f  four launches %.2f   MatMult (L2-warm) %.2f us" % (m, n, len(a), out["1"], out["0"], mm), flush=True)
+    print("m=%4d rows %7d nnz %8d  CG us/iter: persistent %.2f  four launches %.2f  graph replay %.2f   MatMult (L2-warm) %.2f us" % (m, n, len(a), out["persistent"], out["launches"], out["graph"], mm), flush=True)
     del A
 if "cfg" in sys.argv:
     ip, j, a = P.laplace2d_5pt(1000, 1000); n = 10 ** 6
@@ -42,9 +42,8 @@ if "cfg" in sys.argv:
         mm = 1e3 * pb.timer_stop() / 200
         one, b, sol = pb.Vec(n), pb.Vec(n), pb.Vec(n)
         one.set(1.0); A.mult(one, b)
-        os.environ["B200_CG_PERSISTENT"] = "0"
         pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=20, fused=1, histmax=0)
-        r = pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=400, fused=1, check_every=400, histmax=0)
-        print("1000^2 shape %d: MatMult (L2-warm) %.2f us, CG four launches %.2f us/iter  %s" % (cfg, mm, 1e3 * r["solve_ms"] / r["its"], A.bin_info()), flush=True)
+        r = pb.ksp_solve(A, b, sol, ksp_type="cg", pc_type="jacobi", rtol=1e-50, max_it=1280, fused=1, check_every=256, histmax=0)
+        print("1000^2 shape %d: MatMult (L2-warm) %.2f us, CG (graph replay) %.2f us/iter  %s" % (cfg, mm, 1e3 * r["solve_ms"] / r["its"], A.bin_info()), flush=True)
         del A
     pb.spmv_tuning()
