@@ -10,6 +10,8 @@
  */
 #include "b200_internal.h"
 #include <vector>
+#include <thread>
+#include <functional>
 #include <algorithm>
 
 extern "C" int b200_split_ownership(int N, int size, int bs, int *range)
@@ -33,18 +35,32 @@ extern "C" int b200_mpiaij_split(int m, int cstart, int cend, const int *i, cons
 {
   if (m < 0 || !i) return b200_seterr(B200_ERR_ARG_NULL, "bad arguments");
   const long long nz = i[m];
-  long long nzA = 0, nzB = 0;
-  for (long long k = 0; k < nz; k++) {
-    const int c = j[k];
-    if (c >= cstart && c < cend) nzA++; else nzB++;
-  }
-  /* distinct off-process columns, ascending (mmaij.c:42-50 sorts; :80-84 scans ascending — same array) */
-  std::vector<int> g;
-  g.reserve((size_t)std::min<long long>(nzB, 1 << 24));
-  {
-    /* rows are ascending, so per-row runs are sorted: merge by sort+unique of the collected ids in chunks */
-    std::vector<int> buf;
-    buf.reserve(1 << 22);
+  /* Row ranges of about equal entry counts, one host thread each: the split of a 512^3 27-point slab (450 M entries per
+   * rank) is 4 passes over the entries, which one thread takes seconds for.  Every pass below is independent per row, so
+   * the result does not depend on the number of threads. */
+  int T = (int)std::thread::hardware_concurrency();
+  if (T < 1 || nz < (1 << 22)) T = 1;
+  { const char *e = getenv("B200_HOST_THREADS"); if (e && atoi(e) > 0) T = atoi(e); }   /* also forces threads on small inputs (tests) */
+  if (T > 16) T = 16;
+  if (T > m) T = m > 0 ? m : 1;
+  std::vector<int> cut((size_t)T + 1, m);
+  cut[0] = 0;
+  for (int t = 1; t < T; t++) cut[t] = (int)(std::lower_bound(i, i + m + 1, (int)(nz * t / T)) - i);
+  for (int t = 1; t <= T; t++) if (cut[t] < cut[t - 1]) cut[t] = cut[t - 1];
+  auto par = [&](const std::function<void(int)> &f) {
+    if (T == 1) { f(0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(f, t);
+    f(0);
+    for (auto &x : th) x.join();
+  };
+  /* pass 1: entries per row in the diagonal block (Bcount = row length - Acount), and the distinct off-process columns
+   * of each row range (sorted; rows are ascending, chunks are sorted, made unique and merged) */
+  std::vector<int> acnt((size_t)m + 1, 0);
+  std::vector<std::vector<int>> gt((size_t)T);
+  par([&](int t) {
+    std::vector<int> &g = gt[t], buf;
+    buf.reserve(1 << 20);
     auto flush = [&]() {
       std::sort(buf.begin(), buf.end());
       buf.erase(std::unique(buf.begin(), buf.end()), buf.end());
@@ -54,12 +70,30 @@ extern "C" int b200_mpiaij_split(int m, int cstart, int cend, const int *i, cons
       g.swap(merged);
       buf.clear();
     };
-    for (long long k = 0; k < nz; k++) {
-      const int c = j[k];
-      if (c < cstart || c >= cend) { buf.push_back(c); if (buf.size() >= (size_t)(1 << 22)) flush(); }
+    for (int r = cut[t]; r < cut[t + 1]; r++) {
+      int na = 0;
+      for (int k = i[r]; k < i[r + 1]; k++) {
+        const int c = j[k];
+        if (c >= cstart && c < cend) na++;
+        else { buf.push_back(c); if (buf.size() >= (size_t)(1 << 20)) flush(); }
+      }
+      acnt[r] = na;
     }
     flush();
+  });
+  /* distinct off-process columns, ascending (mmaij.c:42-50 sorts; :80-84 scans ascending — same array) */
+  std::vector<int> g;
+  for (int t = 0; t < T; t++) {
+    if (gt[t].empty()) continue;
+    std::vector<int> merged;
+    merged.reserve(g.size() + gt[t].size());
+    std::set_union(g.begin(), g.end(), gt[t].begin(), gt[t].end(), std::back_inserter(merged));
+    g.swap(merged);
+    std::vector<int>().swap(gt[t]);
   }
+  long long nzA = 0;
+  for (int r = 0; r < m; r++) nzA += acnt[r];
+  const long long nzB = nz - nzA;
   const int nghost = (int)g.size();
   if (nzA_out) *nzA_out = nzA;
   if (nzB_out) *nzB_out = nzB;
@@ -67,20 +101,22 @@ extern "C" int b200_mpiaij_split(int m, int cstart, int cend, const int *i, cons
   if (!Ai) return 0;                                   /* size query */
   if (!Aj || !Aa || !Bi || !Bj || !Ba || !garray) return b200_seterr(B200_ERR_ARG_NULL, "null output arrays");
   for (int k = 0; k < nghost; k++) garray[k] = g[k];
-  long long pa = 0, pb = 0;
   Ai[0] = 0; Bi[0] = 0;
-  for (int r = 0; r < m; r++) {
-    for (int k = i[r]; k < i[r + 1]; k++) {
-      const int c = j[k];
-      if (c >= cstart && c < cend) { Aj[pa] = c - cstart; Aa[pa] = a[k]; pa++; }   /* mpiaij.c:515-520 */
-      else {
-        /* compacted id = position in garray (mmaij.c:56-63) */
-        const int lid = (int)(std::lower_bound(g.begin(), g.end(), c) - g.begin());
-        Bj[pb] = lid; Ba[pb] = a[k]; pb++;
+  for (int r = 0; r < m; r++) { Ai[r + 1] = Ai[r] + acnt[r]; Bi[r + 1] = Bi[r] + (i[r + 1] - i[r] - acnt[r]); }
+  /* pass 2: every row writes at its own offsets */
+  par([&](int t) {
+    for (int r = cut[t]; r < cut[t + 1]; r++) {
+      long long pa = Ai[r], pb = Bi[r];
+      for (int k = i[r]; k < i[r + 1]; k++) {
+        const int c = j[k];
+        if (c >= cstart && c < cend) { Aj[pa] = c - cstart; Aa[pa] = a[k]; pa++; }   /* mpiaij.c:515-520 */
+        else {
+          /* compacted id = position in garray (mmaij.c:56-63) */
+          Bj[pb] = (int)(std::lower_bound(g.begin(), g.end(), c) - g.begin()); Ba[pb] = a[k]; pb++;
+        }
       }
     }
-    Ai[r + 1] = (int)pa; Bi[r + 1] = (int)pb;
-  }
+  });
   return 0;
 }
 

@@ -202,3 +202,24 @@ def test_gloo_general_scatter_plan(pb):
             assert list(oto["to_procs"]) == [r]
             assert np.array_equal(oto["to_indices"], bs * inidx[~owned] - ranges[o])
             assert list(oto["to_starts"]) == [0, int((~owned).sum())]
+
+
+def test_split_is_the_same_on_any_number_of_host_threads(monkeypatch):
+    """b200_mpiaij_split works on row ranges in parallel for large inputs; B200_HOST_THREADS forces that path on a small
+    one: diag/off-diag blocks and garray must be identical to the one-thread result."""
+    import importlib
+    par = importlib.import_module("petsc-dev_b200.parallel")
+    P = importlib.import_module("workloads.problems")
+    N = 6000
+    ranges = par.split_ownership(N, 3)
+    for rank in range(3):
+        r0, r1 = int(ranges[rank]), int(ranges[rank + 1])
+        ip, j, a = P.powerlaw(N, r0, r1)
+        ip = (ip - ip[0]).astype(np.int32)
+        monkeypatch.setenv("B200_HOST_THREADS", "1")
+        one = par.mpiaij_split(r1 - r0, r0, r1, ip, j, a)
+        for T in ("2", "7", "16"):
+            monkeypatch.setenv("B200_HOST_THREADS", T)
+            many = par.mpiaij_split(r1 - r0, r0, r1, ip, j, a)
+            for key in one:
+                assert np.array_equal(one[key], many[key]), (rank, T, key)
