@@ -169,6 +169,19 @@ int b200_mat_setvaluesbatch_values(b200_mat A, const double *elem_mats, int on_d
  * exchange of whole elements). */
 int b200_mat_setvaluesbatch_rows(int m_local, int rstart, int N, long long ne, int nl, const int *elem_rows, const double *elem_mats,
                                  int on_device, int keep_plan, b200_mat *A);
+/* The diagonal/off-diagonal split of such local rows ON THE DEVICE (MatSetValues_MPIAIJ routing mpiaij.c:507-565 +
+ * MatSetUpMultiply_MPIAIJ compaction mmaij.c:28-64; the reference's device assembly sorts two COO lists for it,
+ * mpiaijAssemble.cu:200-460): L = the matrix b200_mat_setvaluesbatch_rows returned (kept), [cstart, cend) this rank's
+ * columns.  Only garray (nghost ints) and the two row-offset arrays reach the host.  b200_split_get reads the sizes and
+ * garray (the caller builds the scatter lists from it with b200_scatter_plan_from/_to); b200_mat_create_mpiaij_split is
+ * b200_mat_create_mpiaij with the device blocks of the split, which it consumes. */
+typedef struct b200_split_s *b200_split;
+int b200_mat_split_device(b200_mat L, int cstart, int cend, int *nghost, b200_split *S);
+int b200_split_get(b200_split S, long long *nzA, long long *nzB, int *nghost, int *garray_host);
+int b200_split_destroy(b200_split S);
+int b200_mat_create_mpiaij_split(b200_split S, int N,
+                                 int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                                 int nfrom, const int *from_procs, const int *from_starts, b200_mat *A);
 /* The exchange plan of that step (host integer work, no GPU needed).  b200_batch_send_plan: counts[d] = how many of my
  * elements touch rows of rank d != rank; send_elems (NULL on a sizing call, else sum(counts) entries) = their element
  * numbers grouped by destination ascending.  Every rank publishes one buffer with its groups in that order and the

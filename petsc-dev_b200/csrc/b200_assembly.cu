@@ -549,3 +549,184 @@ extern "C" int b200_mat_get_csr(b200_mat A, int *i, int *j, double *a)
   B200_CUDA(cudaStreamSynchronize(st));
   return 0;
 }
+
+/* ================================================================================================ device-side split
+ * The local rows of a parallel matrix (m rows x N GLOBAL columns, ascending per row — what b200_mat_setvaluesbatch_rows
+ * assembles) split into the diagonal block (columns [cstart, cend) -> local ids) and the compacted off-diagonal block
+ * (columns -> positions in the sorted list of distinct off-process columns, `garray`) WITHOUT a trip through the host:
+ * MatSetValues_MPIAIJ's routing (mpiaij.c:507-565) + MatSetUpMultiply_MPIAIJ's compaction (mmaij.c:28-64), the step the
+ * reference's device assembly does with two COO sorts (mpiaijAssemble.cu:200-460).  No sort here: columns ascend inside a
+ * row, so a row's diagonal-block entries are ONE contiguous run found by two bisections; the distinct off-process columns
+ * are the set bits of an N-bit map (atomicOr), garray is that map read out in order, and an entry's ghost id is the
+ * number of set bits below its column (word prefix + popc) — garray ascending exactly as mmaij.c:50 sorts it.
+ * Only the m+1 row offsets of the two blocks and garray (nghost ints) go to the host: the SpMV row binning and the
+ * scatter plan are built from them. */
+struct b200_split_s {
+  int        m, ncols_local, nghost;
+  long long  nzA, nzB;
+  int       *d_Ai, *d_Aj, *d_Bi, *d_Bj;
+  double    *d_Aa, *d_Ba;
+  int       *h_Ai, *h_Bi, *h_garray;
+};
+
+__device__ __forceinline__ int split_lower_bound(const int *__restrict__ j, int b, int e, int key)
+{
+  while (b < e) { const int mid = (b + e) >> 1; if (__ldg(&j[mid]) < key) b = mid + 1; else e = mid; }
+  return b;
+}
+
+/* one warp per row: run bounds, counts, and the off-process columns marked in the bit map */
+__global__ void __launch_bounds__(256) split_count_kernel(int m, const int *__restrict__ li, const int *__restrict__ lj, int cstart, int cend,
+                                                          int *__restrict__ acnt, int *__restrict__ bcnt, int *__restrict__ runlo, unsigned *bitmap)
+{
+  const int lane = threadIdx.x & 31, nw = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < m; r += nw) {
+    const int b = __ldg(&li[r]), e = __ldg(&li[r + 1]);
+    const int lo = split_lower_bound(lj, b, e, cstart), hi = split_lower_bound(lj, lo, e, cend);
+    if (lane == 0) { acnt[r] = hi - lo; bcnt[r] = (e - b) - (hi - lo); runlo[r] = lo; }
+    for (int k = b + lane; k < lo; k += 32) { const int c = __ldg(&lj[k]); atomicOr(&bitmap[c >> 5], 1u << (c & 31)); }
+    for (int k = hi + lane; k < e; k += 32) { const int c = __ldg(&lj[k]); atomicOr(&bitmap[c >> 5], 1u << (c & 31)); }
+  }
+}
+
+__global__ void split_popc_kernel(int nwords, const unsigned *__restrict__ bitmap, int *__restrict__ wcnt)
+{
+  for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += gridDim.x * blockDim.x) wcnt[w] = __popc(bitmap[w]);
+}
+
+__global__ void split_garray_kernel(int nwords, const unsigned *__restrict__ bitmap, const int *__restrict__ wpre, int *__restrict__ garray)
+{
+  for (int w = blockIdx.x * blockDim.x + threadIdx.x; w < nwords; w += gridDim.x * blockDim.x) {
+    unsigned bits = bitmap[w];
+    int p = wpre[w];
+    while (bits) { const int t = __ffs(bits) - 1; bits &= bits - 1; garray[p++] = w * 32 + t; }
+  }
+}
+
+/* one warp per row: the diagonal run with local column ids, the two off-diagonal runs with ghost ids, values alongside */
+__global__ void __launch_bounds__(256) split_fill_kernel(int m, const int *__restrict__ li, const int *__restrict__ lj, const double *__restrict__ la,
+                                                         int cstart, const int *__restrict__ runlo, const int *__restrict__ Ai, const int *__restrict__ Bi,
+                                                         const unsigned *__restrict__ bitmap, const int *__restrict__ wpre,
+                                                         int *__restrict__ Aj, double *__restrict__ Aa, int *__restrict__ Bj, double *__restrict__ Ba)
+{
+  const int lane = threadIdx.x & 31, nw = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < m; r += nw) {
+    const int b = __ldg(&li[r]), e = __ldg(&li[r + 1]), lo = __ldg(&runlo[r]);
+    const int pa = __ldg(&Ai[r]), na = __ldg(&Ai[r + 1]) - pa, pb = __ldg(&Bi[r]), hi = lo + na;
+    for (int k = lane; k < na; k += 32) { Aj[pa + k] = __ldg(&lj[lo + k]) - cstart; Aa[pa + k] = __ldg(&la[lo + k]); }
+    const int nb = (e - b) - na, nleft = lo - b;
+    for (int k = lane; k < nb; k += 32) {
+      const int src = k < nleft ? b + k : hi + (k - nleft);
+      const int c = __ldg(&lj[src]);
+      Bj[pb + k] = __ldg(&wpre[c >> 5]) + __popc(__ldg(&bitmap[c >> 5]) & ((1u << (c & 31)) - 1u));
+      Ba[pb + k] = __ldg(&la[src]);
+    }
+  }
+}
+
+extern "C" int b200_split_destroy(b200_split S)
+{
+  if (!S) return 0;
+  cudaFree(S->d_Ai); cudaFree(S->d_Aj); cudaFree(S->d_Aa); cudaFree(S->d_Bi); cudaFree(S->d_Bj); cudaFree(S->d_Ba);
+  free(S->h_Ai); free(S->h_Bi); free(S->h_garray);
+  free(S);
+  return 0;
+}
+
+extern "C" int b200_mat_split_device(b200_mat L, int cstart, int cend, int *nghost_out, b200_split *out)
+{
+  B200_NEED_INIT();
+  if (!L || !out) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  *out = NULL;
+  if (L->kind != 0 || L->A.nstrips > 1 || L->A.compressed) return b200_seterr(B200_ERR_ARG_WRONG, "the local rows must be one uncompressed sequential block");
+  const B200Seq *A = &L->A;
+  const int m = A->m, N = A->n;
+  if (cstart < 0 || cend < cstart || cend > N) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "column range [%d,%d) outside [0,%d)", cstart, cend, N);
+  cudaStream_t st = g_b200.stream;
+  DevBufs tmp(st);
+  const int nwords = (N + 31) / 32;
+  int *acnt, *bcnt, *runlo, *wcnt, *wpre;
+  unsigned *bitmap;
+  b200_split S = (b200_split)calloc(1, sizeof(*S));
+  if (!S) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  S->m = m; S->ncols_local = cend - cstart;
+#define SPLIT_FAIL(call) do { cudaError_t e__ = (call); if (e__ != cudaSuccess) { b200_split_destroy(S); return b200_cuda_err(e__, #call, __FILE__, __LINE__); } } while (0)
+  SPLIT_FAIL(tmp.get(&acnt, (size_t)m + 1));
+  SPLIT_FAIL(tmp.get(&bcnt, (size_t)m + 1));
+  SPLIT_FAIL(tmp.get(&runlo, (size_t)m + 1));
+  SPLIT_FAIL(tmp.get(&bitmap, (size_t)nwords + 1));
+  SPLIT_FAIL(tmp.get(&wcnt, (size_t)nwords + 1));
+  SPLIT_FAIL(tmp.get(&wpre, (size_t)nwords + 1));
+  SPLIT_FAIL(tmp.get(&S->d_Ai, (size_t)m + 1)); tmp.release(S->d_Ai);
+  SPLIT_FAIL(tmp.get(&S->d_Bi, (size_t)m + 1)); tmp.release(S->d_Bi);
+  SPLIT_FAIL(cudaMemsetAsync(bitmap, 0, sizeof(unsigned) * ((size_t)nwords + 1), st));
+  const int gw = m > 0 ? (m + 7) / 8 : 1;                 /* 8 warps per CTA */
+  split_count_kernel<<<gw > B200_NSM * 16 ? B200_NSM * 16 : gw, 256, 0, st>>>(m, A->d_i, A->d_j, cstart, cend, acnt, bcnt, runlo, bitmap);
+  split_popc_kernel<<<grid_for(nwords, 256), 256, 0, st>>>(nwords, bitmap, wcnt);
+  g_b200.launches += 2;
+  int rc = dev_exclusive_scan(m, acnt, S->d_Ai, tmp, st);
+  if (!rc) rc = dev_exclusive_scan(m, bcnt, S->d_Bi, tmp, st);
+  if (!rc) rc = dev_exclusive_scan(nwords, wcnt, wpre, tmp, st);
+  if (rc) { b200_split_destroy(S); return rc; }
+  S->h_Ai = (int *)malloc(sizeof(int) * ((size_t)m + 1));
+  S->h_Bi = (int *)malloc(sizeof(int) * ((size_t)m + 1));
+  if (!S->h_Ai || !S->h_Bi) { b200_split_destroy(S); return b200_seterr(B200_ERR_MEM, "out of host memory"); }
+  int ng = 0;
+  SPLIT_FAIL(cudaMemcpyAsync(S->h_Ai, S->d_Ai, sizeof(int) * ((size_t)m + 1), cudaMemcpyDeviceToHost, st));
+  SPLIT_FAIL(cudaMemcpyAsync(S->h_Bi, S->d_Bi, sizeof(int) * ((size_t)m + 1), cudaMemcpyDeviceToHost, st));
+  SPLIT_FAIL(cudaMemcpyAsync(&ng, wpre + nwords, sizeof(int), cudaMemcpyDeviceToHost, st));
+  SPLIT_FAIL(cudaStreamSynchronize(st));
+  S->nzA = S->h_Ai[m]; S->nzB = S->h_Bi[m]; S->nghost = ng;
+  int *d_garray;
+  SPLIT_FAIL(tmp.get(&d_garray, (size_t)ng + 1));
+  SPLIT_FAIL(tmp.get(&S->d_Aj, (size_t)S->nzA + 8)); tmp.release(S->d_Aj);
+  SPLIT_FAIL(tmp.get(&S->d_Aa, (size_t)S->nzA + 8)); tmp.release(S->d_Aa);
+  SPLIT_FAIL(tmp.get(&S->d_Bj, (size_t)S->nzB + 8)); tmp.release(S->d_Bj);
+  SPLIT_FAIL(tmp.get(&S->d_Ba, (size_t)S->nzB + 8)); tmp.release(S->d_Ba);
+  split_garray_kernel<<<grid_for(nwords, 256), 256, 0, st>>>(nwords, bitmap, wpre, d_garray);
+  split_fill_kernel<<<gw > B200_NSM * 16 ? B200_NSM * 16 : gw, 256, 0, st>>>(m, A->d_i, A->d_j, A->d_a, cstart, runlo, S->d_Ai, S->d_Bi, bitmap, wpre,
+                                                                             S->d_Aj, S->d_Aa, S->d_Bj, S->d_Ba);
+  g_b200.launches += 2;
+  S->h_garray = (int *)malloc(sizeof(int) * ((size_t)ng + 1));
+  if (!S->h_garray) { b200_split_destroy(S); return b200_seterr(B200_ERR_MEM, "out of host memory"); }
+  SPLIT_FAIL(cudaMemcpyAsync(S->h_garray, d_garray, sizeof(int) * (size_t)ng, cudaMemcpyDeviceToHost, st));
+  SPLIT_FAIL(cudaStreamSynchronize(st));
+  SPLIT_FAIL(cudaGetLastError());
+#undef SPLIT_FAIL
+  if (nghost_out) *nghost_out = ng;
+  *out = S;
+  return 0;
+}
+
+extern "C" int b200_split_get(b200_split S, long long *nzA, long long *nzB, int *nghost, int *garray_host)
+{
+  if (!S) return b200_seterr(B200_ERR_ARG_NULL, "null split");
+  if (nzA) *nzA = S->nzA;
+  if (nzB) *nzB = S->nzB;
+  if (nghost) *nghost = S->nghost;
+  if (garray_host && S->nghost) memcpy(garray_host, S->h_garray, sizeof(int) * (size_t)S->nghost);
+  return 0;
+}
+
+/* b200_mat_create_mpiaij with the two blocks taken from the split (consumed: S is destroyed, also on failure) */
+extern "C" int b200_mat_create_mpiaij_split(b200_split S, int N,
+                                            int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                                            int nfrom, const int *from_procs, const int *from_starts, b200_mat *Aout)
+{
+  B200_NEED_INIT();
+  if (!S || !Aout) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  *Aout = NULL;
+  b200_mat M = (b200_mat)calloc(1, sizeof(*M));
+  if (!M) { b200_split_destroy(S); return b200_seterr(B200_ERR_MEM, "out of host memory"); }
+  M->kind = 1;
+  int rc = b200_seq_adopt(&M->A, S->m, S->ncols_local, S->h_Ai, S->d_Ai, S->d_Aj, S->d_Aa);
+  S->d_Ai = NULL; S->d_Aj = NULL; S->d_Aa = NULL;          /* owned by the block from here on, also on failure */
+  if (!rc) {
+    rc = b200_seq_adopt(&M->B, S->m, S->nghost, S->h_Bi, S->d_Bi, S->d_Bj, S->d_Ba);
+    S->d_Bi = NULL; S->d_Bj = NULL; S->d_Ba = NULL;
+  }
+  if (rc) { b200_mat_destroy(M); b200_split_destroy(S); return rc; }
+  rc = b200_mpiaij_finish(M, N, S->nghost, S->h_Bi, S->h_garray, nto, to_procs, to_starts, to_indices, nfrom, from_procs, from_starts, Aout);
+  b200_split_destroy(S);
+  return rc;
+}

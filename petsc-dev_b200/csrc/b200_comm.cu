@@ -537,22 +537,14 @@ static int peerplan_build(b200_mat M)
   return b200_comm_barrier();
 }
 
-extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
-                                      const int *Ai, const int *Aj, const double *Aa,
-                                      int nghost, const int *Bi, const int *Bj, const double *Ba, const int *garray,
-                                      int nto, const int *to_procs, const int *to_starts, const int *to_indices,
-                                      int nfrom, const int *from_procs, const int *from_starts,
-                                      b200_mat *Aout)
+/* the part of MatCreate_MPIAIJ + MatSetUpMultiply that follows the two blocks: scatter lists, ghost buffers (peer arena or
+ * plain), pack list, the one-launch plan.  M->A and M->B are in place (uploaded or adopted); M is destroyed on failure. */
+int b200_mpiaij_finish(b200_mat M, int N, int nghost, const int *Bi, const int *garray,
+                       int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                       int nfrom, const int *from_procs, const int *from_starts, b200_mat *Aout)
 {
-  B200_NEED_INIT();
-  if (!Aout) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
-  *Aout = NULL;
-  b200_mat M = (b200_mat)calloc(1, sizeof(*M));
-  if (!M) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  int rc = 0;
   M->kind = 1; M->N = N; M->nghost = nghost; M->nto = nto; M->nfrom = nfrom;
-  int rc = b200_seq_upload(&M->A, m, n_local, Ai, Aj, Aa);
-  if (!rc) rc = b200_seq_upload(&M->B, m, nghost, Bi, Bj, Ba);
-  if (rc) { b200_mat_destroy(M); return rc; }
   if ((nto > 0 && (!to_procs || !to_starts || !to_indices)) || (nfrom > 0 && (!from_procs || !from_starts)) || (nghost > 0 && !garray)) {
     b200_mat_destroy(M);
     return b200_seterr(B200_ERR_ARG_NULL, "null scatter list with nto %d, nfrom %d, nghost %d", nto, nfrom, nghost);
@@ -585,6 +577,25 @@ extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
   if (M->peerplan) { rc = fusedplan_build(M, Bi); if (rc) { b200_mat_destroy(M); return rc; } }
   *Aout = M;
   return 0;
+}
+
+extern "C" int b200_mat_create_mpiaij(int m, int n_local, int N,
+                                      const int *Ai, const int *Aj, const double *Aa,
+                                      int nghost, const int *Bi, const int *Bj, const double *Ba, const int *garray,
+                                      int nto, const int *to_procs, const int *to_starts, const int *to_indices,
+                                      int nfrom, const int *from_procs, const int *from_starts,
+                                      b200_mat *Aout)
+{
+  B200_NEED_INIT();
+  if (!Aout) return b200_seterr(B200_ERR_ARG_NULL, "null output handle");
+  *Aout = NULL;
+  b200_mat M = (b200_mat)calloc(1, sizeof(*M));
+  if (!M) return b200_seterr(B200_ERR_MEM, "out of host memory");
+  M->kind = 1; M->N = N; M->nghost = nghost; M->nto = nto; M->nfrom = nfrom;
+  int rc = b200_seq_upload(&M->A, m, n_local, Ai, Aj, Aa);
+  if (!rc) rc = b200_seq_upload(&M->B, m, nghost, Bi, Bj, Ba);
+  if (rc) { b200_mat_destroy(M); return rc; }
+  return b200_mpiaij_finish(M, N, nghost, Bi, garray, nto, to_procs, to_starts, to_indices, nfrom, from_procs, from_starts, Aout);
 }
 
 /* ------------------------------------------------------------------------------------------------ one-launch MatMult */

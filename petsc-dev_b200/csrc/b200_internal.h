@@ -119,6 +119,8 @@ struct b200_mat_s {
 
 int  b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const double *a);
 int  b200_seq_adopt(B200Seq *S, int m, int n, const int *i_host, int *d_i, int *d_j, double *d_a);
+int  b200_mpiaij_finish(b200_mat M, int N, int nghost, const int *Bi, const int *garray, int nto, const int *to_procs, const int *to_starts,
+                        const int *to_indices, int nfrom, const int *from_procs, const int *from_starts, b200_mat *Aout);
 void *b200_pinned_scratch(size_t bytes);   /* one growing pinned host buffer for short-lived read-backs (single host thread per rank) */
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);

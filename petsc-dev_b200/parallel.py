@@ -112,7 +112,14 @@ def setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=1, dist=None, device
     rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
     m = rend - rstart
     sp = mpiaij_split(m, rstart, rend, ai, aj, aa)
-    g = sp["garray"]
+    return dict(plan_from_garray(rank, size, ranges, sp["garray"], N, bs=bs, dist=dist, device=device), split=sp)
+
+
+def plan_from_garray(rank, size, ranges, garray, N, bs=1, dist=None, device="cpu"):
+    """The VecScatter of MatSetUpMultiply_MPIAIJ (mmaij.c:106-161) from the ghost column list alone."""
+    rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
+    m = rend - rstart
+    g = _i32(garray)
     blk = use_block_is(g, bs)
     if blk:                                                # ISCreateBlock(bs, ec/bs, garray[i*bs]/bs), mmaij.c:130-136
         inidx = (g[::bs] // bs).astype(np.int32)
@@ -126,7 +133,7 @@ def setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=1, dist=None, device
     else:
         procs, lengths, req = np.zeros(0, np.int32), np.zeros(0, np.int32), np.zeros(0, np.int32)
     to = scatter_plan_to(procs, lengths, req, rstart, rend)
-    return dict(split=sp, from_=frm, to=to, bs=pbs, m=m, rstart=rstart, rend=rend, N=int(N), block_is=blk)
+    return dict(from_=frm, to=to, bs=pbs, m=m, rstart=rstart, rend=rend, N=int(N), block_is=blk)
 
 
 def expand_bs(starts, indices, bs):
@@ -310,16 +317,48 @@ def batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist=None, devi
     return np.concatenate(out_r).reshape(-1), np.concatenate(out_m).reshape(-1)
 
 
-def set_values_batch_mpiaij(rank, size, ranges, N, nl, elem_rows, elem_mats, bs=1, dist=None, device="cpu", return_host=False):
+def split_device(L, cstart, cend):
+    """b200_mat_split_device: (handle, nzA, nzB, garray) of the local-rows matrix L, blocks stay on the device."""
+    S, ng = C.c_void_p(), C.c_int()
+    _chk(lib.b200_mat_split_device(L.h, int(cstart), int(cend), C.byref(ng), C.byref(S)), "MatSetUpMultiply (device split)")
+    nzA, nzB = C.c_longlong(), C.c_longlong()
+    g = np.zeros(max(ng.value, 1), np.int32)
+    _chk(lib.b200_split_get(S, C.byref(nzA), C.byref(nzB), C.byref(ng), _ip(g)), "b200_split_get")
+    return S, nzA.value, nzB.value, g[:ng.value]
+
+
+def create_mpiaij_from_split(S, plan):
+    """b200_mat_create_mpiaij_split: the operator from the device blocks of `S` (consumed) and the scatter plan."""
+    frm, to, bs = plan["from_"], plan["to"], plan["bs"]
+    ts, ti = expand_bs(to["to_starts"], to["to_indices"], bs)
+    fs, _ = expand_bs(frm["from_starts"], frm["from_indices"], bs)
+    tp, fp = _i32(to["to_procs"]), _i32(frm["from_procs"])
+    h = C.c_void_p()
+    _chk(lib.b200_mat_create_mpiaij_split(S, int(plan["N"]), int(to["nto"]), _ip(tp), _ip(ts), _ip(ti),
+                                          int(frm["nfrom"]), _ip(fp), _ip(fs), C.byref(h)), "MatAssemblyEnd_MPIAIJ (device blocks)")
+    return Mat(h, plan["m"], plan["m"])
+
+
+def set_values_batch_mpiaij(rank, size, ranges, N, nl, elem_rows, elem_mats, bs=1, dist=None, device="cpu", return_host=False,
+                            device_split=True):
     """MatSetValuesBatch + MatAssemblyBegin/End on a parallel matrix: exchange the interface elements, assemble this
     rank's rows on the device (b200_mat_setvaluesbatch_rows: local rows x global columns), split into the diagonal
-    and off-diagonal blocks and build the ghost exchange exactly as for any other MPIAIJ matrix."""
+    and off-diagonal blocks and build the ghost exchange exactly as for any other MPIAIJ matrix.  device_split: the
+    split happens on the device too (b200_mat_split_device; only garray and row offsets reach the host); otherwise the
+    local rows are read back and split by b200_mpiaij_split."""
     rows, mats = batch_exchange(rank, size, ranges, elem_rows, elem_mats, nl, dist, device)
     rstart, rend = int(ranges[rank]), int(ranges[rank + 1])
     h = C.c_void_p()
     _chk(lib.b200_mat_setvaluesbatch_rows(rend - rstart, rstart, int(N), C.c_longlong(rows.size // nl), int(nl), _ip(rows), _dp(mats),
                                           0, 0, C.byref(h)), "MatSetValuesBatch (local rows)")
     L = Mat(h, rend - rstart, int(N))
+    if device_split:
+        S, _, _, g = split_device(L, rstart, rend)
+        host_csr = L.csr() if return_host else None
+        L.destroy()
+        plan = plan_from_garray(rank, size, ranges, g, N, bs=bs, dist=dist, device=device)
+        A = create_mpiaij_from_split(S, plan)
+        return (A, host_csr) if return_host else A
     ai, aj, aa = L.csr()
     L.destroy()
     host = setup_mpiaij_host(rank, size, ranges, ai, aj, aa, N, bs=bs, dist=dist, device=device)
