@@ -37,6 +37,8 @@ EXAMPLES = {  # unmodified reference programs used by tests/test_gpu_plugin.py
     "b200_scatter_cases": os.path.join(ROOT, "tests", "c", "scatter_cases.c"),
     # VecGetArrayRead between device operations: one download, no upload
     "b200_coherence_seam": os.path.join(ROOT, "tests", "c", "coherence_seam.c"),
+    # MatSetValues into rows other ranks own: the stash path of MatAssemblyBegin/End under the new types
+    "b200_stash_offproc": os.path.join(ROOT, "tests", "c", "stash_offproc.c"),
 }
 
 

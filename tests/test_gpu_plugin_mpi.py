@@ -178,3 +178,23 @@ def test_vec_ex22_parallel_to_parallel_on_the_device():
     assert dev >= 4 and host == 0, (dev, host)
     plain = "\n".join(l for l in got.splitlines() if not (l.startswith("[") and "] " in l and not l.split("] ", 1)[1][:1].isdigit()))
     same_text(plain, json.load(open(GOLD))["src/vec/vec/examples/tests/output/ex22_1.out"], ignore=("type:",))
+
+
+@pytest.mark.parametrize("np_", [1, 2, 3, 4])
+def test_offprocess_matsetvalues_through_the_stash(np_):
+    """tests/c/stash_offproc.c: ADD_VALUES into rows other ranks own (MatSetValues_MPIAIJ -> MatStash -> MatAssemblyEnd,
+    mpiaij.c:496-570, inherited host code), two assemblies — the second one adds new nonzeros and ghost columns on three or
+    more ranks, so the device copy must be rebuilt — MatMult and MatMultTranspose after each: same output as the reference types."""
+    need(np_)
+    want = launch(np_, "b200_stash_offproc", ["-mat_type", "aij"])
+    got = launch(np_, "b200_stash_offproc", B200)
+    same_text(got, want, ignore=("type:",))
+    assert "after assembly 1" in want
+
+
+def test_mat_ex5_on_three_ranks_golden():
+    """the reference's own mat ex5 on 3 ranks (MatMult, MatMultAdd, MatMultTranspose[Add] — the reverse ADD exchange —,
+    MatGetDiagonal, MatDiagonalScale) with the B200 types against its committed golden output ex5_23.out"""
+    need(3)
+    got = launch(3, "mat_ex5", ["-dll_prepend", PLUGIN, "-mat_type", "mpiaijb200", "-vec_type", "mpib200"])
+    same_text(got, json.load(open(GOLD))["src/mat/examples/tests/output/ex5_23.out"], ignore=("type:",))
