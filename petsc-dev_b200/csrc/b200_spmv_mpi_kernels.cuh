@@ -86,11 +86,15 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
   };
   if (tid == 0 && t < ntiles) issue(__ldg(&a.tiles[t]));        /* the first tile streams in while phase 0 runs */
 
-  /* ---- phase 0: VecScatterBegin ---- */
-  if ((int)blockIdx.x < a.npack) {
+  /* ---- phase 0: VecScatterBegin ----
+   * done by the LAST npack CTAs of the grid: the tile walk is round-robin, so when the tile count is not a multiple of the
+   * grid the first CTAs carry one tile more — the packing CTAs should be the others (one tile is ~4 us, about what the
+   * gather + system fence of phase 0 costs; measured with the first CTAs packing: the kernel's tail grew by that much) */
+  const int pk = (int)blockIdx.x - ((int)gridDim.x - a.npack);
+  if (pk >= 0) {
     const PeerPlanDev &plan = a.plan;
     /* credits first (stream order: this rank's previous product, which read the other parity's buffer, is complete) */
-    if (blockIdx.x == 0 && tid < plan.nfrom) st_release_sys(plan.rcredit[tid], a.epoch - 1);
+    if (pk == 0 && tid < plan.nfrom) st_release_sys(plan.rcredit[tid], a.epoch - 1);
     if (tid <= plan.nto) s_starts[tid] = plan.to_starts[tid];
     if (tid < plan.nto) {
       s_dst[tid] = plan.dst[a.parity * plan.nto + tid];
@@ -98,7 +102,7 @@ spmv_mpiaij_kernel(const MpiSpmvArgs a)
     }
     __syncthreads();
     int k = 0;
-    for (int i = blockIdx.x * THREADS + tid; i < a.nsend; i += a.npack * THREADS) {
+    for (int i = pk * THREADS + tid; i < a.nsend; i += a.npack * THREADS) {
       while (i >= s_starts[k + 1]) k++;
       s_dst[k][i - s_starts[k]] = __ldg(&a.x[__ldg(&a.to_idx[i])]);
     }
