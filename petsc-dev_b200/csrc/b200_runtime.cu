@@ -259,14 +259,17 @@ extern "C" int b200_memset(void *dst, int byte, size_t bytes)
 struct UpWorker { cudaStream_t st; void *buf[2]; cudaEvent_t ev[2]; bool ready; };
 static UpWorker g_up[B200_UP_MAXW];
 static int      g_up_max = 0;
+static char    *g_up_pinned = NULL;        /* ONE pinned block for all workers' buffers: every cudaHostAlloc call has a
+                                              fixed cost of milliseconds (16 calls were ~70 ms of the first big upload) */
 
-/* workers are set up one by one as uploads need them (pinning host memory is slow: 2 MB per worker, ~2 ms each) */
+/* workers (stream + two events) are set up as uploads need them */
 static int up_worker_init(int k)
 {
   if (g_up[k].ready) return 0;
+  if (!g_up_pinned) B200_CUDA(cudaHostAlloc((void **)&g_up_pinned, (size_t)B200_UP_MAXW * 2 * B200_UP_CHUNK, cudaHostAllocDefault));
   B200_CUDA(cudaStreamCreateWithFlags(&g_up[k].st, cudaStreamNonBlocking));
   for (int b = 0; b < 2; b++) {
-    B200_CUDA(cudaHostAlloc(&g_up[k].buf[b], B200_UP_CHUNK, cudaHostAllocDefault));
+    g_up[k].buf[b] = g_up_pinned + ((size_t)k * 2 + b) * B200_UP_CHUNK;
     B200_CUDA(cudaEventCreateWithFlags(&g_up[k].ev[b], cudaEventDisableTiming));
   }
   g_up[k].ready = true;
@@ -306,9 +309,10 @@ void b200_upload_release(void)
   for (int k = 0; k < B200_UP_MAXW; k++) {
     if (!g_up[k].ready) continue;
     cudaStreamDestroy(g_up[k].st);
-    for (int b = 0; b < 2; b++) { cudaFreeHost(g_up[k].buf[b]); cudaEventDestroy(g_up[k].ev[b]); }
+    for (int b = 0; b < 2; b++) cudaEventDestroy(g_up[k].ev[b]);
     g_up[k].ready = false;
   }
+  if (g_up_pinned) { cudaFreeHost(g_up_pinned); g_up_pinned = NULL; }
 }
 
 int b200_upload_pageable(void *dst, const void *src, size_t bytes)
