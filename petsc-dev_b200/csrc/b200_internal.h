@@ -81,6 +81,7 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
   int       *d_longstart;     /* [nlong+1] first chunk slot of each long row                                          */
   double    *d_longpart;      /* [nchunks] per-chunk partial sums                                                     */
   double    *d_dotpart;       /* [grid + nlong] per-CTA partials of the fused x.y                                    */
+  unsigned  *d_ticket;        /* last-CTA ticket of the DOT variants' CG tail                                         */
   int       *d_diagpos;       /* [m] position of a_ii in d_a or -1 (Mat_SeqAIJ::diag, aij.c:1486 MatMarkDiagonal_SeqAIJ);
                                  recorded by the first MatGetDiagonal, kept across value-only refreshes               */
   /* column strips (cache blocking for matrices whose x gathers would not stay in L2): when nstrips > 1 the block is
@@ -124,7 +125,9 @@ int  b200_mpiaij_finish(b200_mat M, int N, int nghost, const int *Bi, const int 
 void *b200_pinned_scratch(size_t bytes);   /* one growing pinned host buffer for short-lived read-backs (single host thread per rank) */
 void b200_seq_free(B200Seq *S);
 int  b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out);
-int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out);
+struct CgState;
+int  b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out,
+                      CgState *cg = NULL);   /* cg: the kernel's last CTA also takes the CG scalar step after p.w (fused CG on one GPU) */
 int  b200_seq_transpose(B200Seq *S);
 void b200_seq_dotparts(const B200Seq *S, const double **p, int *n);
 int  b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out);

@@ -484,7 +484,11 @@ static int cg_fused(b200_mat A, const Pc *pc, Conv *cv, int max_it, int check_ev
       CgAr ar1 = {0, NULL, c.rank, 1}, ar2 = {0, NULL, c.rank, 1};
       CgParts parts = {NULL, 0, NULL, 0};
       bool dot_done = false;                      /* p.w, its allreduce and the scalar step after it already ran */
-      if (seq) {
+      if (seq && !multi && A->A.nlong == 0 && A->A.ntiles > 0) {
+        /* one GPU: the product's last CTA finishes p.w and takes the scalar step — three launches per iteration */
+        rc = b200_seq_mult_ex(&A->A, P, NULL, W, false, true, P, NULL, ds); if (rc) goto done;
+        dot_done = true;
+      } else if (seq) {
         rc = b200_seq_mult_ex(&A->A, P, NULL, W, false, true, P, NULL); if (rc) goto done;
         b200_seq_dotparts(&A->A, &parts.a, &parts.na);
       } else if (mpi_dot && b200_mpiaij_fused(A)) {

@@ -16,6 +16,8 @@
  */
 #include "b200_internal.h"
 #include <vector>
+#include <thread>
+#include <functional>
 #include <algorithm>
 #include <math.h>
 
@@ -103,7 +105,7 @@ void b200_seq_free(B200Seq *S)
   }
   if (S->d_ci && S->d_ci != S->d_i) cudaFree(S->d_ci);
   cudaFree(S->d_i); cudaFree(S->d_j); cudaFree(S->d_a); cudaFree(S->d_rindex);
-  cudaFree(S->d_diagpos); cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
+  cudaFree(S->d_ticket); cudaFree(S->d_diagpos); cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
   memset(S, 0, sizeof(*S));
 }
 
@@ -272,6 +274,8 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
     B200_CUDA(cudaMalloc((void **)&S->d_longpart, sizeof(double) * (size_t)nchunks));
   }
   B200_CUDA(cudaMalloc((void **)&S->d_dotpart, sizeof(double) * ((size_t)S->grid + S->nlong + 1)));
+  B200_CUDA(cudaMalloc((void **)&S->d_ticket, sizeof(unsigned)));
+  B200_CUDA(cudaMemset(S->d_ticket, 0, sizeof(unsigned)));
   return 0;
 }
 
@@ -325,24 +329,52 @@ int b200_seq_upload(B200Seq *S, int m, int n, const int *i, const int *j, const 
     for (int r = 0; r < m; r++) if (i[r + 1] < i[r]) return b200_seterr(B200_ERR_ARG_WRONG, "row offsets decrease at row %d", r);
   }
   S->nonzerorow = nonempty;
-  std::vector<int> si((size_t)m + 1), sj;
+  /* per strip: count every row's entries below the strip's upper column bound, prefix-sum, copy — the counting and the
+   * copying on row ranges in parallel (a 500 M-entry matrix took 4 s on one thread); the result is the same whatever
+   * the number of threads */
+  int T = (int)std::thread::hardware_concurrency();
+  if (T < 1 || nz < (1 << 22)) T = 1;
+  { const char *e = getenv("B200_HOST_THREADS"); if (e && atoi(e) > 0) T = atoi(e); }
+  if (T > 16) T = 16;
+  if (T > m) T = m > 0 ? m : 1;
+  std::vector<int> cut((size_t)T + 1, m);
+  cut[0] = 0;
+  for (int t = 1; t < T; t++) cut[t] = (int)(std::lower_bound(i, i + m + 1, (int)(nz * t / T)) - i);
+  for (int t = 1; t <= T; t++) if (cut[t] < cut[t - 1]) cut[t] = cut[t - 1];
+  auto par = [&](const std::function<void(int)> &f) {
+    if (T == 1) { f(0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < T; t++) th.emplace_back(f, t);
+    f(0);
+    for (auto &x : th) x.join();
+  };
+  std::vector<int> si((size_t)m + 1), sj, cur(i, i + m), nxt((size_t)m);   /* cur: next unread entry of every row */
   std::vector<double> sa;
-  std::vector<int> cur(i, i + m);                         /* next unread entry of every row */
   for (int k = 0; k < ns; k++) {
     const long long chi = (long long)(k + 1) * width;
-    sj.clear(); sa.clear();
+    par([&](int t) {
+      for (int r = cut[t]; r < cut[t + 1]; r++) {
+        int c = cur[r];
+        const int e = i[r + 1];
+        while (c < e && (long long)j[c] < chi) c++;
+        nxt[r] = c;
+      }
+    });
     si[0] = 0;
-    for (int r = 0; r < m; r++) {
-      int c = cur[r];
-      const int e = i[r + 1];
-      const int b = c;
-      while (c < e && (long long)j[c] < chi) c++;
-      sj.insert(sj.end(), j + b, j + c);
-      sa.insert(sa.end(), a + b, a + c);
-      cur[r] = c;
-      si[r + 1] = (int)sj.size();
-    }
-    S->strip_nzoff[k + 1] = S->strip_nzoff[k] + (long long)sj.size();
+    for (int r = 0; r < m; r++) si[(size_t)r + 1] = si[r] + (nxt[r] - cur[r]);
+    const size_t snz = (size_t)si[m];
+    sj.resize(snz); sa.resize(snz);
+    par([&](int t) {
+      for (int r = cut[t]; r < cut[t + 1]; r++) {
+        const int b = cur[r], len = nxt[r] - b;
+        if (len > 0) {
+          memcpy(sj.data() + si[r], j + b, sizeof(int) * (size_t)len);
+          memcpy(sa.data() + si[r], a + b, sizeof(double) * (size_t)len);
+        }
+        cur[r] = nxt[r];
+      }
+    });
+    S->strip_nzoff[k + 1] = S->strip_nzoff[k] + (long long)snz;
     int rc = seq_upload_one(&S->strips[k], m, n, si.data(), sj.data(), sa.data());
     if (rc) return rc;
   }
@@ -412,14 +444,14 @@ int b200_seq_transpose(B200Seq *S)
 
 /* ---- tile-kernel dispatch: (launch shape) x (lanes per row) x (add, dot) */
 template <int G, bool PARK, int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
+static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, const SpmvCgTail &tail, cudaStream_t st)
 {
   const size_t smem = SpmvSmem<THREADS, TILE_NNZ, STAGES>::BYTES;
 #define GO(ADD, DOT) do { \
     auto kern = spmv_tile_kernel<G, PARK, ADD, DOT, THREADS, TILE_NNZ, STAGES>; \
     static bool attr_done = false; \
     if (!attr_done) { cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); if (e != cudaSuccess) return e; attr_done = true; } \
-    kern<<<S->grid, THREADS, smem, st>>>(S->ntiles, S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart, S->d_longpart, dotx); \
+    kern<<<S->grid, THREADS, smem, st>>>(S->ntiles, S->d_tiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_dotpart, S->d_longpart, dotx, tail); \
   } while (0)
   if (add) { if (dot) GO(true, true); else GO(true, false); }
   else     { if (dot) GO(false, true); else GO(false, false); }
@@ -428,50 +460,52 @@ static cudaError_t launch_tile5(const B200Seq *S, bool add, bool dot, const doub
 }
 
 template <int G, int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile4(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
+static cudaError_t launch_tile4(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, const SpmvCgTail &tail, cudaStream_t st)
 {
-  return S->park ? launch_tile5<G, true, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st)
-                 : launch_tile5<G, false, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+  return S->park ? launch_tile5<G, true, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st)
+                 : launch_tile5<G, false, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
 }
 
 template <int THREADS, int TILE_NNZ, int STAGES>
-static cudaError_t launch_tile3(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
+static cudaError_t launch_tile3(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, const SpmvCgTail &tail, cudaStream_t st)
 {
   switch (S->G) {
-    case 1:  return launch_tile4<1,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
-    case 2:  return launch_tile4<2,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
-    case 4:  return launch_tile4<4,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
-    case 8:  return launch_tile4<8,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
-    case 16: return launch_tile4<16, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
-    default: return launch_tile4<32, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, st);
+    case 1:  return launch_tile4<1,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 2:  return launch_tile4<2,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 4:  return launch_tile4<4,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 8:  return launch_tile4<8,  THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 16: return launch_tile4<16, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
+    default: return launch_tile4<32, THREADS, TILE_NNZ, STAGES>(S, add, dot, x, yin, z, dotx, tail, st);
   }
 }
 
-static cudaError_t launch_tile(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, cudaStream_t st)
+static cudaError_t launch_tile(const B200Seq *S, bool add, bool dot, const double *x, const double *yin, double *z, const double *dotx, const SpmvCgTail &tail, cudaStream_t st)
 {
   switch (S->cfg) {                       /* must mirror g_cfgs[] */
-    case 0:  return launch_tile3<256, 2048, 1>(S, add, dot, x, yin, z, dotx, st);
-    case 1:  return launch_tile3<256, 2048, 2>(S, add, dot, x, yin, z, dotx, st);
-    case 2:  return launch_tile3<512, 4096, 2>(S, add, dot, x, yin, z, dotx, st);
-    case 3:  return launch_tile3<128, 1024, 1>(S, add, dot, x, yin, z, dotx, st);
-    case 4:  return launch_tile3<512, 4096, 1>(S, add, dot, x, yin, z, dotx, st);
-    case 5:  return launch_tile3<256, 1792, 2>(S, add, dot, x, yin, z, dotx, st);
-    case 6:  return launch_tile3<256, 4096, 2>(S, add, dot, x, yin, z, dotx, st);
-    default: return launch_tile3<384, 3072, 1>(S, add, dot, x, yin, z, dotx, st);
+    case 0:  return launch_tile3<256, 2048, 1>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 1:  return launch_tile3<256, 2048, 2>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 2:  return launch_tile3<512, 4096, 2>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 3:  return launch_tile3<128, 1024, 1>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 4:  return launch_tile3<512, 4096, 1>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 5:  return launch_tile3<256, 1792, 2>(S, add, dot, x, yin, z, dotx, tail, st);
+    case 6:  return launch_tile3<256, 4096, 2>(S, add, dot, x, yin, z, dotx, tail, st);
+    default: return launch_tile3<384, 3072, 1>(S, add, dot, x, yin, z, dotx, tail, st);
   }
 }
 
 /* z = (add ? yin : 0) + S x.  want_dot: the CTAs leave partials of dotx . (z - yin) in S->d_dotpart (dotx NULL = x);
  * dot_out (device scalar), when non-NULL, receives their sum (one more tiny kernel). */
-int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out)
+int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, double *z, bool add, bool want_dot, const double *dotx, double *dot_out, CgState *cg)
 {
   cudaStream_t st = g_b200.stream;
   if (S->m == 0) return 0;
+  if (cg && (!want_dot || S->nlong || S->nstrips > 1 || !S->ntiles)) return b200_seterr(B200_ERR_SUP, "the CG tail needs the fused dot on a block without long rows or strips");
+  const SpmvCgTail tail = {cg, S->d_ticket};
   if (S->nstrips > 1) {
     if (want_dot) return b200_seterr(B200_ERR_SUP, "fused dot is not available for a column-stripped block");
     for (int k = 0; k < S->nstrips; k++) {
       /* the first strip starts the row sums (from 0 or from yin), every later one continues them in place */
-      B200_CHK(b200_seq_mult_ex(&S->strips[k], x, k == 0 ? yin : z, z, k == 0 ? add : true, false, NULL, NULL));
+      B200_CHK(b200_seq_mult_ex(&S->strips[k], x, k == 0 ? yin : z, z, k == 0 ? add : true, false, NULL, NULL, NULL));
     }
     return 0;
   }
@@ -486,7 +520,7 @@ int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doubl
   }
   if (want_dot && S->compressed && !add) return b200_seterr(B200_ERR_SUP, "fused dot needs an uncompressed block (or the MatMultAdd form)");
   if (S->ntiles) {
-    B200_CUDA(launch_tile(S, add, want_dot, x, yin, z, dotx, st));
+    B200_CUDA(launch_tile(S, add, want_dot, x, yin, z, dotx, tail, st));
     B200_LAUNCHED(1);
   }
   if (S->nlong) {
@@ -514,7 +548,7 @@ void b200_seq_dotparts(const B200Seq *S, const double **p, int *n)
 
 int b200_seq_mult(const B200Seq *S, const double *x, const double *yin, double *z, bool add, double *dot_out)
 {
-  return b200_seq_mult_ex(S, x, yin, z, add, dot_out != NULL, NULL, dot_out);
+  return b200_seq_mult_ex(S, x, yin, z, add, dot_out != NULL, NULL, dot_out, NULL);
 }
 
 /* y = A x on the row-partitioned operator with the LOCAL part of x . y left in dot_out (device scalar): the diagonal
@@ -533,9 +567,9 @@ int b200_mpiaij_mult_dot(b200_mat A, const double *x, double *y, double *dot_out
   }
   if (Sa->compressed || Sa->m != Sa->n || Sa->nstrips > 1 || Sb->nstrips > 1) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square, uncompressed, unstripped diagonal block");
   B200_CHK(b200_mpiaij_exchange_begin(A, x));
-  B200_CHK(b200_seq_mult_ex(Sa, x, NULL, y, false, true, x, NULL));
+  B200_CHK(b200_seq_mult_ex(Sa, x, NULL, y, false, true, x, NULL, NULL));
   B200_CHK(b200_mpiaij_exchange_end(A));
-  B200_CHK(b200_seq_mult_ex(Sb, A->d_lvec[A->epoch & 1], y, y, true, true, x, NULL));
+  B200_CHK(b200_seq_mult_ex(Sb, A->d_lvec[A->epoch & 1], y, y, true, true, x, NULL, NULL));
   if (Sa->m == 0 || !dot_out) return 0;                          /* dot_out NULL: the caller reduces the partial lists itself */
   const int na = (Sa->ntiles ? Sa->grid : 0) + Sa->nlong, nb = (Sb->ntiles ? Sb->grid : 0) + Sb->nlong;
   dot_final_kernel<<<1, 1024, 0, g_b200.stream>>>(na, Sa->ntiles ? Sa->d_dotpart : Sa->d_dotpart + Sa->grid,

@@ -23,6 +23,7 @@
 #define B200_SPMV_KERNELS_CUH
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include "b200_ksp_state.h"     /* CgState + the scalar step the DOT variants can take in their last CTA */
 
 #define SPMV_ALIGN_PAD 8      /* entries of slack per stage: the bulk copies start/end on 4-entry boundaries */
 
@@ -72,6 +73,9 @@ struct SpmvSmem {
  * the ld.global.nc loads for comparison. */
 static __constant__ int b200_c_gather_cg;
 
+/* optional tail of the DOT variants: the CG state whose scalar step the kernel's last CTA takes (NULL: none) */
+struct SpmvCgTail { CgState *cg; unsigned *ticket; };
+
 /* tiles[t] = {row_begin, row_end, k_begin, k_end} in visiting order (ci = offsets in visiting order; rindex maps a
  * visiting position to the row id when the block is stored compressed, else NULL). */
 /* the default shape (256 lanes, one stage) is held to 32 registers = 8 resident CTAs per SM in every variant: at 40
@@ -81,7 +85,7 @@ __global__ void __launch_bounds__(THREADS, (THREADS == 256 && STAGES == 1) ? ((A
 spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
                  const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
                  const double *yin, double *z, double *__restrict__ dotpart, double *__restrict__ longpart,
-                 const double *__restrict__ dotx)
+                 const double *__restrict__ dotx, const SpmvCgTail tail)
 {
   /* DOT: the CTA leaves its share of dotx . (z - yin) in dotpart (dotx == x, yin == 0 for the plain MatMult; for the
    * off-diagonal MatMultAdd dotx is the LOCAL vector, so that diag + off-diag partials add up to x . (A x)) */
@@ -249,6 +253,31 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
       if (lane == 0) dotpart[blockIdx.x] = v;
+    }
+    if (tail.cg) {
+      /* fused CG on one GPU: the last CTA to get here sums the partials of p.w (the order cg_after_dot_kernel uses) and
+       * takes the scalar step that follows the product (cg.c:207-220) — one launch less per iteration */
+      __shared__ bool s_last;
+      if (tid == 0) { __threadfence(); s_last = (atomicAdd(tail.ticket, 1u) == gridDim.x - 1u); }
+      __syncthreads();
+      if (s_last) {                                          /* CTA-uniform */
+        __threadfence();
+        double u = 0.0;
+        for (int i = tid; i < (int)gridDim.x; i += THREADS) u += __ldcg(&dotpart[i]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+        __syncthreads();
+        if (lane == 0) s_red[wid] = u;
+        __syncthreads();
+        if (tid == 0) {
+          double w = 0.0;
+#pragma unroll
+          for (int q = 0; q < THREADS / 32; q++) w += s_red[q];
+          tail.cg->red[3] = w;
+          *tail.ticket = 0;
+          if (tail.cg->reason == 0) cg_after_dot_body(tail.cg);
+        }
+      }
     }
   }
 }
