@@ -208,10 +208,12 @@ def test_full_size_c2_properties(gpu, P):
 
 @pytest.mark.parametrize("strips", [2, 3, 7])
 @pytest.mark.parametrize("name", ["lap7", "plaw", "lap2d_rect"])
-def test_column_strips(gpu, R, P, name, strips):
+def test_column_strips(gpu, R, P, name, strips, monkeypatch):
     """Column-strip storage (cache blocking of x for matrices with scattered columns): y = S_0 x; y += S_1 x; ... With one
     lane per row the row sum is still ONE left-to-right chain -> bit-identical to MatMult_SeqAIJ; the diagonal is
-    collected from the strip that owns it; KSP on a stripped operator follows the reference history."""
+    collected from the strip that owns it; KSP on a stripped operator follows the reference history.  The strips are cut
+    on row ranges by several host threads (forced here on a small matrix)."""
+    monkeypatch.setenv("B200_HOST_THREADS", "3" if strips % 2 else "5")
     if name == "lap7":
         m = n = 12 ** 3
         ip, j, a = P.laplace3d_7pt(12)
