@@ -401,7 +401,13 @@ template <int K>
 static int red_launch(int n, const double *x, const double *y, double *out)
 {
   const bool v2 = aligned16(x) && (!y || aligned16(y));
-  const int g = b200_red_grid(v2 ? (n + 1) / 2 : n, RED_THREADS, 4);
+  int g = b200_red_grid(v2 ? (n + 1) / 2 : n, RED_THREADS, 4);
+  {
+    /* resident CTAs: 2048 / RED_THREADS per SM.  B200_RED_WAVES (experiment): cap the grid at that many waves */
+    static int waves = -1;
+    if (waves < 0) { const char *e = getenv("B200_RED_WAVES"); waves = e ? atoi(e) : 0; }
+    if (waves > 0) { const int cap = g_b200.nsm * (2048 / RED_THREADS) * waves; if (g > cap) g = cap; }
+  }
   if (v2) red_kernel<K, true><<<g, RED_THREADS, 0, g_b200.stream>>>(n, x, y, g_b200.d_partials, g_b200.d_ticket, out);
   else    red_kernel<K, false><<<g, RED_THREADS, 0, g_b200.stream>>>(n, x, y, g_b200.d_partials, g_b200.d_ticket, out);
   B200_LAUNCHED(1);
