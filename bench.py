@@ -474,7 +474,7 @@ def run_b200(args):
                 "gflops": (2.0 * cfg["nnz"] - cfg["rows"]) / (ms_step * 1e-3) / 1e9,
                 "roofline": {"bound": "hbm", "achieved": per_gpu, "peak": peak, "unit": "GB/s", "frac": per_gpu / peak,
                              "traffic": traffic, "traffic_source": traffic_src,
-                             "kernel": ("spmv_tile_kernel<G=1,PARK=0,ADD=0,DOT=0,256,2048,1>" if world == 1 else
+                             "kernel": ("spmv_tile_kernel<G=1,PARK=0,ADD=0,DOT=0,256,2048,1>" if (world == 1 or not transport.startswith("NVLink")) else
                                         "spmv_mpiaij_kernel<G=1,ADD=0,DOT=0,256,2048> (MatMult_MPIAIJ in one launch: ghost exchange, diagonal block, boundary rows)"),
                              "frac_of_nominal_8TBs": per_gpu / 8000.0,
                              "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 (of fallback)",
