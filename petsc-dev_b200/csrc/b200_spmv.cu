@@ -112,6 +112,17 @@ void b200_seq_free(B200Seq *S)
 /* i is a host array.  j / a are host arrays that are copied, unless adopt: then they are device arrays of nz + 8
  * entries (cudaMalloc'ed by the caller, e.g. the device assembly) whose ownership passes to S, and d_i_adopt — the
  * device copy of i the caller already has, m + 1 entries — is adopted as well instead of being uploaded again. */
+static int g_park_cap = 32;
+
+extern "C" int b200_spmv_set_park_cap(int cap)
+{
+  B200_NEED_INIT();
+  g_park_cap = cap;
+  B200_CUDA(cudaStreamSynchronize(g_b200.stream));
+  B200_CUDA(cudaMemcpyToSymbol(b200_c_park_cap, &g_park_cap, sizeof(int)));
+  return 0;
+}
+
 static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, const double *a, bool adopt = false, int *d_i_adopt = NULL)
 {
   memset(S, 0, sizeof(*S));
@@ -121,6 +132,7 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
       const char *e = getenv("B200_SPMV_GATHER_CG");
       const int v = e ? atoi(e) : 1;
       B200_CUDA(cudaMemcpyToSymbol(b200_c_gather_cg, &v, sizeof(int)));
+      B200_CUDA(cudaMemcpyToSymbol(b200_c_park_cap, &g_park_cap, sizeof(int)));
       gather_mode_set = true;
     }
   }

@@ -72,6 +72,9 @@ struct SpmvSmem {
  * 0.799 ms with ld.global.nc on the 2 M-row power-law sample.  B200_SPMV_GATHER_CG=0 (read once in b200_spmv.cu) restores
  * the ld.global.nc loads for comparison. */
 static __constant__ int b200_c_gather_cg;
+/* entries of a row its own lane sums in the parked (irregular-matrix) variant before the row's warp takes over; <= 0: the
+ * lane sums the whole row (b200_spmv_set_park_cap, set from b200_spmv.cu) */
+static __constant__ int b200_c_park_cap;
 
 /* optional tail of the DOT variants: the CG state whose scalar step the kernel's last CTA takes (NULL: none) */
 struct SpmvCgTail { CgState *cg; unsigned *ticket; };
@@ -195,16 +198,46 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
           }
           __syncthreads();
         }
-        if (G == 1) {
+        if (G == 1 && PARK) {
+          /* Row sums from the parked products.  One lane per row sums left to right — but only the first PARK_CAP entries:
+           * with power-law row lengths a tile's longest row (up to the long-row threshold, 256) used to keep 255 lanes
+           * waiting at the barrier below for one serial chain of shared-memory loads (ncu, C4: 37 % of the warp samples
+           * at the two barriers, 11 % in this loop, 40 % in the gathers).  What a row has beyond PARK_CAP entries its WARP
+           * sums together: lanes stride the rest (consecutive addresses, no bank conflicts), a shuffle tree, the row's lane
+           * adds it on.  Rows of up to PARK_CAP entries keep the reference's order exactly. */
+          const int PARK_CAP = b200_c_park_cap > 0 ? b200_c_park_cap : 0x7fffffff;
+          const int lane = tid & 31;
+          const int len = e_cur - b_cur;                    /* 0 for lanes without a row */
+          double sum = ADD ? y_cur : 0.0;
+          {
+            const int e1 = b_cur + (len < PARK_CAP ? len : PARK_CAP);
+#pragma unroll 4
+            for (int k = b_cur; k < e1; k++) sum += sa[k];
+          }
+          unsigned more = __ballot_sync(0xffffffffu, len > PARK_CAP);
+          while (more) {
+            const int src = __ffs(more) - 1;
+            more &= more - 1;
+            const int bb = __shfl_sync(0xffffffffu, b_cur, src) + PARK_CAP, ee = __shfl_sync(0xffffffffu, e_cur, src);
+            double part = 0.0;
+            for (int k = bb + lane; k < ee; k += 32) part += sa[k];
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+            if (lane == src) sum += part;
+          }
+          if (row_cur >= 0) {
+            z[row_cur] = sum;
+            if (DOT) {
+              const double xd = __ldg(&dotx[row_cur]);
+              dot += xd * sum;
+              if (ADD) dot -= xd * y_cur;
+            }
+          }
+        } else if (G == 1) {
           if (row_cur >= 0) {
             double sum = ADD ? y_cur : 0.0;
-            if (PARK) {
 #pragma unroll 4
-              for (int k = b_cur; k < e_cur; k++) sum += sa[k];
-            } else {
-#pragma unroll 4
-              for (int k = b_cur; k < e_cur; k++) sum += sa[k] * __ldg(&x[sj[k]]);
-            }
+            for (int k = b_cur; k < e_cur; k++) sum += sa[k] * __ldg(&x[sj[k]]);
             z[row_cur] = sum;
             if (DOT) {
               const double xd = __ldg(&dotx[row_cur]);
