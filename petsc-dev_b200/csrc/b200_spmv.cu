@@ -203,6 +203,10 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
     if (g_tune_park >= 0) S->park = g_tune_park != 0;
     S->long_thresh = g_cfgs[cfg].tile_nnz < 64 * G ? g_cfgs[cfg].tile_nnz : 64 * G;
     if (S->long_thresh < 256) S->long_thresh = 256 < g_cfgs[cfg].tile_nnz ? 256 : g_cfgs[cfg].tile_nnz;
+    /* parked variant with one lane per row: a long row no longer holds its tile up (the row's warp sums what exceeds the
+     * cap, b200_spmv_set_park_cap), so only rows that do not fit a tile are cut into chunk tiles — C4: 3565 such rows
+     * instead of 84 746, 3.81 -> 3.63 ms per product (profiles/r02_plaw_sweep_cap_10M.txt) */
+    if (S->park && G == 1 && g_park_cap > 0) S->long_thresh = g_cfgs[cfg].tile_nnz;
     const char *el = getenv("B200_SPMV_LONG");
     if (el && atoi(el) > 0 && atoi(el) <= g_cfgs[cfg].tile_nnz) S->long_thresh = atoi(el);
     if (g_tune_long > 0 && g_tune_long <= g_cfgs[cfg].tile_nnz) S->long_thresh = g_tune_long;
