@@ -212,7 +212,9 @@ int b200_mat_bin_info2(b200_mat A, int *lanes_per_row, int *long_thresh, int *gr
  * and whether products are parked in shared memory before the row sums (the choice for irregular row lengths). */
 int b200_spmv_set_tuning(int shape, int lanes_per_row, int long_thresh, int park);
 /* Parked (irregular-matrix) variant: how many entries of a row its own lane sums left to right before the row's warp sums
- * the rest together (default 32; <= 0: the lane sums the whole row, the round-1 behaviour).  Takes effect at once. */
+ * the rest together (default 32; <= 0: the lane sums the whole row, the round-1 behaviour).  For matrices created AFTER
+ * the call, and only where the binning chose one lane per row by itself: lanes_per_row = 1 REQUESTED through
+ * b200_spmv_set_tuning always means the reference's left-to-right order for every row. */
 int b200_spmv_set_park_cap(int cap);
 /* Column strips (cache blocking of the x gathers) for matrices created AFTER the call: -1 = automatic (strips of ~24 MB
  * of x when x exceeds 48 MB and the mean row spans more than a strip), 0/1 = off, k = force k strips.  With one lane

@@ -116,10 +116,7 @@ static int g_park_cap = 32;
 
 extern "C" int b200_spmv_set_park_cap(int cap)
 {
-  B200_NEED_INIT();
   g_park_cap = cap;
-  B200_CUDA(cudaStreamSynchronize(g_b200.stream));
-  B200_CUDA(cudaMemcpyToSymbol(b200_c_park_cap, &g_park_cap, sizeof(int)));
   return 0;
 }
 
@@ -132,7 +129,6 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
       const char *e = getenv("B200_SPMV_GATHER_CG");
       const int v = e ? atoi(e) : 1;
       B200_CUDA(cudaMemcpyToSymbol(b200_c_gather_cg, &v, sizeof(int)));
-      B200_CUDA(cudaMemcpyToSymbol(b200_c_park_cap, &g_park_cap, sizeof(int)));
       gather_mode_set = true;
     }
   }
@@ -206,7 +202,8 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
     /* parked variant with one lane per row: a long row no longer holds its tile up (the row's warp sums what exceeds the
      * cap, b200_spmv_set_park_cap), so only rows that do not fit a tile are cut into chunk tiles — C4: 3565 such rows
      * instead of 84 746, 3.81 -> 3.63 ms per product (profiles/r02_plaw_sweep_cap_10M.txt) */
-    if (S->park && G == 1 && g_park_cap > 0) S->long_thresh = g_cfgs[cfg].tile_nnz;
+    S->park_cap = (S->park && G == 1 && S->req_G != 1 && g_park_cap > 0) ? g_park_cap : 0;   /* an explicit request for one lane per row keeps the reference order */
+    if (S->park_cap > 0) S->long_thresh = g_cfgs[cfg].tile_nnz;            /* the explicit settings below still override */
     const char *el = getenv("B200_SPMV_LONG");
     if (el && atoi(el) > 0 && atoi(el) <= g_cfgs[cfg].tile_nnz) S->long_thresh = atoi(el);
     if (g_tune_long > 0 && g_tune_long <= g_cfgs[cfg].tile_nnz) S->long_thresh = g_tune_long;
@@ -516,7 +513,7 @@ int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doubl
   cudaStream_t st = g_b200.stream;
   if (S->m == 0) return 0;
   if (cg && (!want_dot || S->nlong || S->nstrips > 1 || !S->ntiles)) return b200_seterr(B200_ERR_SUP, "the CG tail needs the fused dot on a block without long rows or strips");
-  const SpmvCgTail tail = {cg, S->d_ticket};
+  const SpmvCgTail tail = {cg, S->d_ticket, S->park_cap};
   if (S->nstrips > 1) {
     if (want_dot) return b200_seterr(B200_ERR_SUP, "fused dot is not available for a column-stripped block");
     for (int k = 0; k < S->nstrips; k++) {

@@ -72,12 +72,12 @@ struct SpmvSmem {
  * 0.799 ms with ld.global.nc on the 2 M-row power-law sample.  B200_SPMV_GATHER_CG=0 (read once in b200_spmv.cu) restores
  * the ld.global.nc loads for comparison. */
 static __constant__ int b200_c_gather_cg;
-/* entries of a row its own lane sums in the parked (irregular-matrix) variant before the row's warp takes over; <= 0: the
- * lane sums the whole row (b200_spmv_set_park_cap, set from b200_spmv.cu) */
-static __constant__ int b200_c_park_cap;
 
-/* optional tail of the DOT variants: the CG state whose scalar step the kernel's last CTA takes (NULL: none) */
-struct SpmvCgTail { CgState *cg; unsigned *ticket; };
+/* per-launch extras.  cg/ticket: optional tail of the DOT variants — the CG state whose scalar step the kernel's last CTA
+ * takes (NULL: none).  park_cap: parked (irregular-matrix) variant with one lane per row — how many entries of a row its own
+ * lane sums before the row's warp takes over; <= 0: the lane sums the whole row, i.e. the reference's left-to-right order for
+ * every row (what a caller who ASKED for one lane per row gets: b200_spmv_set_tuning(lanes_per_row = 1)). */
+struct SpmvCgTail { CgState *cg; unsigned *ticket; int park_cap; };
 
 /* tiles[t] = {row_begin, row_end, k_begin, k_end} in visiting order (ci = offsets in visiting order; rindex maps a
  * visiting position to the row id when the block is stored compressed, else NULL). */
@@ -204,8 +204,9 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
            * waiting at the barrier below for one serial chain of shared-memory loads (ncu, C4: 37 % of the warp samples
            * at the two barriers, 11 % in this loop, 40 % in the gathers).  What a row has beyond PARK_CAP entries its WARP
            * sums together: lanes stride the rest (consecutive addresses, no bank conflicts), a shuffle tree, the row's lane
-           * adds it on.  Rows of up to PARK_CAP entries keep the reference's order exactly. */
-          const int PARK_CAP = b200_c_park_cap > 0 ? b200_c_park_cap : 0x7fffffff;
+           * adds it on.  Rows of up to PARK_CAP entries keep the reference's order exactly; so does every row when the
+           * caller asked for one lane per row (tail.park_cap == 0). */
+          const int PARK_CAP = tail.park_cap > 0 ? tail.park_cap : 0x7fffffff;
           const int lane = tid & 31;
           const int len = e_cur - b_cur;                    /* 0 for lanes without a row */
           double sum = ADD ? y_cur : 0.0;
