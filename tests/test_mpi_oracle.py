@@ -138,3 +138,19 @@ def test_reference_goldens_on_more_than_one_rank(case):
 @pytest.mark.parametrize("n", [1, 2, 5, 8])
 def test_shim_selftest(n):
     assert "b200mpi selftest ok %d" % n in mpirun(n, "mpishim_selftest")
+
+
+@needs_mpi_oracle
+@pytest.mark.parametrize("prog,ranks", [("b200_scatter_cases", (1, 2, 3)), ("b200_stash_offproc", (1, 2, 3, 4)), ("b200_coherence_seam", (1,))])
+def test_plugin_test_programs_run_on_the_reference_types(prog, ranks):
+    """The repository's own PETSc programs behind the GPU plugin tests (tests/c/*.c, public API only) must run under the
+    reference's CPU types on every rank count the GPU tests use, and print the same text twice: they are the 'want' side of
+    those tests (tests/test_gpu_plugin_mpi.py)."""
+    if not os.path.exists(os.path.join(BIN, prog)):
+        pytest.skip("%s not built (petsc-dev_b200/plugin/build_plugin.py)" % prog)
+    for n in ranks:
+        a = mpirun(n, prog, ["-mat_type", "aij"] if "stash" in prog else [])
+        b = mpirun(n, prog, ["-mat_type", "aij"] if "stash" in prog else [])
+        assert a == b and len(a.splitlines()) >= 2, (prog, n)
+        if prog == "b200_scatter_cases":
+            assert a.count("forward") + a.count("reverse") == 19          # the 19 scatters the device test counts
