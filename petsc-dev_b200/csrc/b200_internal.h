@@ -81,6 +81,11 @@ struct B200Seq {              /* one CSR block on the device + its row binning  
   int       *d_longstart;     /* [nlong+1] first chunk slot of each long row                                          */
   double    *d_longpart;      /* [nchunks] per-chunk partial sums                                                     */
   double    *d_dotpart;       /* [grid + nlong] per-CTA partials of the fused x.y                                    */
+  /* warp-tile form of an irregular block (spmv_warp_kernel): its own tile table and long-row chunks (256 entries each)     */
+  int        nwtiles, nwlong, nwchunks;
+  int4      *d_wtiles;
+  int       *d_wlong, *d_wlongstart;
+  double    *d_wlongpart;
   int        park_cap;        /* parked variant: entries a row's own lane sums before its warp takes over (0: all)  */
   unsigned  *d_ticket;        /* last-CTA ticket of the DOT variants' CG tail                                         */
   int       *d_diagpos;       /* [m] position of a_ii in d_a or -1 (Mat_SeqAIJ::diag, aij.c:1486 MatMarkDiagonal_SeqAIJ);

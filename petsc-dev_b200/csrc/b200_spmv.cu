@@ -105,6 +105,7 @@ void b200_seq_free(B200Seq *S)
   }
   if (S->d_ci && S->d_ci != S->d_i) cudaFree(S->d_ci);
   cudaFree(S->d_i); cudaFree(S->d_j); cudaFree(S->d_a); cudaFree(S->d_rindex);
+  cudaFree(S->d_wtiles); cudaFree(S->d_wlong); cudaFree(S->d_wlongstart); cudaFree(S->d_wlongpart);
   cudaFree(S->d_ticket); cudaFree(S->d_diagpos); cudaFree(S->d_tiles); cudaFree(S->d_long); cudaFree(S->d_longstart); cudaFree(S->d_longpart); cudaFree(S->d_dotpart);
   memset(S, 0, sizeof(*S));
 }
@@ -202,8 +203,8 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
     /* parked variant with one lane per row: a long row no longer holds its tile up (the row's warp sums what exceeds the
      * cap, b200_spmv_set_park_cap), so only rows that do not fit a tile are cut into chunk tiles — C4: 3565 such rows
      * instead of 84 746, 3.81 -> 3.63 ms per product (profiles/r02_plaw_sweep_cap_10M.txt) */
-    S->park_cap = (S->park && G == 1 && S->req_G != 1 && g_park_cap > 0) ? g_park_cap : 0;   /* an explicit request for one lane per row keeps the reference order */
-    if (S->park_cap > 0) S->long_thresh = g_cfgs[cfg].tile_nnz;            /* the explicit settings below still override */
+    S->park_cap = (S->park && S->req_G <= 0 && g_park_cap > 0) ? g_park_cap : 0;   /* an explicit request for a number of lanes per row (1 = the reference order) is honoured as it is */
+    if (S->park_cap > 0 && G == 1) S->long_thresh = g_cfgs[cfg].tile_nnz;  /* the explicit settings below still override */
     const char *el = getenv("B200_SPMV_LONG");
     if (el && atoi(el) > 0 && atoi(el) <= g_cfgs[cfg].tile_nnz) S->long_thresh = atoi(el);
     if (g_tune_long > 0 && g_tune_long <= g_cfgs[cfg].tile_nnz) S->long_thresh = g_tune_long;
@@ -289,6 +290,45 @@ static int seq_upload_one(B200Seq *S, int m, int n, const int *i, const int *j, 
   B200_CUDA(cudaMalloc((void **)&S->d_dotpart, sizeof(double) * ((size_t)S->grid + S->nlong + 1)));
   B200_CUDA(cudaMalloc((void **)&S->d_ticket, sizeof(unsigned)));
   B200_CUDA(cudaMemset(S->d_ticket, 0, sizeof(unsigned)));
+  /* the warp-tile form for irregular blocks with one lane per row (B200_SPMV_WARP=0 keeps the CTA-tile form) */
+  {
+    const char *ew = getenv("B200_SPMV_WARP");
+    const bool want = S->park_cap > 0 && nz > 0 && !(ew && !atoi(ew));
+    if (want) {
+      std::vector<int4> wt;
+      std::vector<int>  wl, wls;
+      int wts = 0, wch = 0;
+      wt.reserve((size_t)(nz / SPMV_WARP_TILE) * 2 + 16);
+      auto wclose = [&](int re) { if (re > wts) wt.push_back(make_int4(wts, re, vi[wts], vi[re])); };
+      for (int r = 0; r < nrows; r++) {
+        const int len = vi[r + 1] - vi[r];
+        if (len > SPMV_WARP_TILE) {
+          wclose(r);
+          wl.push_back(r); wls.push_back(wch);
+          for (int kb = vi[r]; kb < vi[r + 1]; kb += SPMV_WARP_TILE) {
+            const int ke = kb + SPMV_WARP_TILE < vi[r + 1] ? kb + SPMV_WARP_TILE : vi[r + 1];
+            wt.push_back(make_int4(r, -(wch + 1), kb, ke));
+            wch++;
+          }
+          wts = r + 1;
+          continue;
+        }
+        if (vi[r + 1] - vi[wts] > SPMV_WARP_TILE || r - wts >= 32) { wclose(r); wts = r; }
+      }
+      wclose(nrows);
+      wls.push_back(wch);
+      S->nwtiles = (int)wt.size(); S->nwlong = (int)wl.size(); S->nwchunks = wch;
+      B200_CUDA(cudaMalloc((void **)&S->d_wtiles, sizeof(int4) * (wt.size() + 1)));
+      B200_CUDA(cudaMemcpy(S->d_wtiles, wt.data(), sizeof(int4) * wt.size(), cudaMemcpyHostToDevice));
+      if (S->nwlong) {
+        B200_CUDA(cudaMalloc((void **)&S->d_wlong, sizeof(int) * wl.size()));
+        B200_CUDA(cudaMemcpy(S->d_wlong, wl.data(), sizeof(int) * wl.size(), cudaMemcpyHostToDevice));
+        B200_CUDA(cudaMalloc((void **)&S->d_wlongstart, sizeof(int) * wls.size()));
+        B200_CUDA(cudaMemcpy(S->d_wlongstart, wls.data(), sizeof(int) * wls.size(), cudaMemcpyHostToDevice));
+        B200_CUDA(cudaMalloc((void **)&S->d_wlongpart, sizeof(double) * (size_t)(wch + 1)));
+      }
+    }
+  }
   return 0;
 }
 
@@ -532,6 +572,21 @@ int b200_seq_mult_ex(const B200Seq *S, const double *x, const double *yin, doubl
     B200_LAUNCHED(1);
   }
   if (want_dot && S->compressed && !add) return b200_seterr(B200_ERR_SUP, "fused dot needs an uncompressed block (or the MatMultAdd form)");
+  if (S->nwtiles && !want_dot) {
+    /* irregular block, plain product: one warp per 256-entry tile, no CTA barriers (spmv_warp_kernel) */
+    int g = (S->nwtiles + 7) / 8;
+    if (g > g_b200.nsm * 6) g = g_b200.nsm * 6;
+    if (add) spmv_warp_kernel<true><<<g, 256, 0, st>>>(S->nwtiles, S->d_wtiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_wlongpart, S->park_cap);
+    else     spmv_warp_kernel<false><<<g, 256, 0, st>>>(S->nwtiles, S->d_wtiles, S->d_ci, S->d_rindex, S->d_j, S->d_a, x, yin, z, S->d_wlongpart, S->park_cap);
+    B200_LAUNCHED(1);
+    if (S->nwlong) {
+      const int fg = (S->nwlong + 127) / 128;
+      if (add) spmv_long_finish_kernel<true, false><<<fg, 128, 0, st>>>(S->nwlong, S->d_wlong, S->d_wlongstart, S->d_rindex, S->d_wlongpart, dotx, yin, z, NULL);
+      else     spmv_long_finish_kernel<false, false><<<fg, 128, 0, st>>>(S->nwlong, S->d_wlong, S->d_wlongstart, S->d_rindex, S->d_wlongpart, dotx, yin, z, NULL);
+      B200_LAUNCHED(1);
+    }
+    return 0;
+  }
   if (S->ntiles) {
     B200_CUDA(launch_tile(S, add, want_dot, x, yin, z, dotx, tail, st));
     B200_LAUNCHED(1);

@@ -316,6 +316,81 @@ spmv_tile_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restri
   }
 }
 
+/* ---- irregular matrices: one WARP per tile, no CTA-wide barrier ------------------------------------------------------
+ * The CTA-tile kernel above meets two barriers per tile in its parked form, and a microbenchmark of exactly that form with
+ * perfectly balanced rows (tools/gather_peak.cu) tops out at 105-120 G gathers/s against 275 G/s for a kernel that only
+ * gathers: the phases serialise inside a CTA.  Here a tile is at most 256 entries / 32 whole rows and belongs to one warp:
+ * lanes load ids and values coalesced straight from global memory (streaming loads), keep 8 gathers of x each in flight,
+ * leave the products in the warp's 2 KB of shared memory, and after a __syncwarp every row's lane sums its row left to right
+ * (up to `cap` entries; what a row has beyond that the warp sums together, as in the parked CTA form).  The 64 warps of an
+ * SM drift apart, so the load/store path always has gathers to do.  Rows longer than a tile are cut into 256-entry chunks,
+ * one warp and one partial each, summed in chunk order by spmv_long_finish_kernel. */
+#define SPMV_WARP_TILE 256
+template <bool ADD>
+__global__ void __launch_bounds__(256, 6)
+spmv_warp_kernel(int ntiles, const int4 *__restrict__ tiles, const int *__restrict__ ci, const int *__restrict__ rindex,
+                 const int *__restrict__ aj, const double *__restrict__ aa, const double *__restrict__ x,
+                 const double *yin, double *z, double *__restrict__ longpart, int cap)
+{
+  __shared__ double s_p[8][SPMV_WARP_TILE];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  double *sp = s_p[wid];
+  const int nw = gridDim.x * 8;
+  const int CAP = cap > 0 ? cap : 0x7fffffff;
+  for (int t = blockIdx.x * 8 + wid; t < ntiles; t += nw) {
+    const int4 d = __ldg(&tiles[t]);                         /* warp-uniform */
+    const int k0 = d.z, n = d.w - d.z;
+    /* this lane's row (row tiles only): bounds relative to the tile, fetched before the gathers so that everything is in flight together */
+    int b = 0, e = 0, row = -1;
+    double y0 = 0.0;
+    if (d.y >= 0 && lane < d.y - d.x) {
+      const int pos = d.x + lane;
+      b = __ldg(&ci[pos]) - k0; e = __ldg(&ci[pos + 1]) - k0;
+      row = rindex ? __ldg(&rindex[pos]) : pos;
+      if (ADD) y0 = yin[row];
+    }
+    int c[8];
+    double v[8];
+#pragma unroll
+    for (int u = 0; u < 8; u++) { const int k = lane + 32 * u; c[u] = k < n ? __ldcs(&aj[k0 + k]) : -1; }
+#pragma unroll
+    for (int u = 0; u < 8; u++) { const int k = lane + 32 * u; v[u] = k < n ? __ldcs(&aa[k0 + k]) : 0.0; }
+#pragma unroll
+    for (int u = 0; u < 8; u++) v[u] = c[u] >= 0 ? v[u] * __ldcg(&x[c[u]]) : 0.0;
+    if (d.y < 0) {
+      /* chunk of a long row: fixed-shape tree over the 256 products, partial -> longpart[slot] */
+      double s = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+      if (lane == 0) longpart[-d.y - 1] = s;
+      continue;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; u++) sp[lane + 32 * u] = v[u];
+    __syncwarp();
+    const int len = e - b;
+    double sum = ADD ? y0 : 0.0;
+    {
+      const int e1 = b + (len < CAP ? len : CAP);
+#pragma unroll 4
+      for (int k = b; k < e1; k++) sum += sp[k];
+    }
+    unsigned more = __ballot_sync(0xffffffffu, len > CAP);
+    while (more) {
+      const int src = __ffs(more) - 1;
+      more &= more - 1;
+      const int bb = __shfl_sync(0xffffffffu, b, src) + CAP, ee = __shfl_sync(0xffffffffu, e, src);
+      double part = 0.0;
+      for (int k = bb + lane; k < ee; k += 32) part += sp[k];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+      if (lane == src) sum += part;
+    }
+    if (row >= 0) z[row] = sum;
+    __syncwarp();                                            /* the next tile overwrites sp */
+  }
+}
+
 /* long rows: sum the chunk partials of each row in chunk order (fixed association), add y, write z (+ the x.z term) */
 template <bool ADD, bool DOT>
 __global__ void __launch_bounds__(128)
