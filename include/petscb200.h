@@ -134,6 +134,15 @@ int b200_vec_norm_local(int n, const double *x, int normtype, double *result_hos
 int b200_vec_mdot(int n, const double *x, int nv, const double *const *y_host_ptrs, double *result_host); /* VecMDot_Seq dvec2.c:146 / _MPI */
 int b200_vec_mdot_local(int n, const double *x, int nv, const double *const *y_host_ptrs, double *result_host);
 int b200_vec_dotnorm2(int n, const double *s, const double *t, double *dp_host, double *nm_host);  /* VecDotNorm2, veccusp.cu:1816 */
+/* b200_vec_mdot_noalloc: NO counterpart in the reference — added for callers
+ * that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  The b200_vec_mdot_local
+ * kernel with its partial-sum scratch in a static device array (148.25 KB, held by every GPU that loads the library
+ * until exit): it calls no cudaMalloc/cudaFree or allocating routine and does not need b200_init.  z_dev[0..nv) is a
+ * DEVICE buffer of the caller; the work is queued on cuda_stream (a cudaStream_t; NULL = the library's stream after
+ * b200_init, else the default stream) and nothing synchronises.  Limits: nv <= 16, n <= 2^30 — beyond them
+ * B200_ERR_ARG_SIZ.  All calls on a device share the scratch: calls that overlap on the GPU (streams with no
+ * ordering between them) race; calls on one stream do not.  Same grid and summation order as b200_vec_mdot_local. */
+int b200_vec_mdot_noalloc(int n, const double *x, int nv, const double *const *y_host_ptrs, double *z_dev, void *cuda_stream);
 
 /* ---- Mat (AIJ / CSR) ------------------------------------------------------------------------------------------
  * b200_mat_create_seqaij uploads an ASSEMBLED host CSR (Mat_SeqAIJ i/j/a, src/mat/impls/aij/seq/aij.h:10-39; column

@@ -239,6 +239,13 @@ class Vec:
         _chk(f(self.n, self.p, nv, tab, _dp(z)), "VecMDot")
         return z[:nv]
 
+    def mdot_noalloc(self, ys, z_dev, stream=None):
+        """b200_vec_mdot_noalloc: VecMDot with static device scratch; z_dev is a device Vec of >= len(ys) entries.
+        Queued on the library's stream (or the cudaStream_t given); nothing is read back here."""
+        nv = len(ys)
+        tab = (c_dp * max(nv, 1))(*[y.p for y in ys])
+        _chk(lib.b200_vec_mdot_noalloc(self.n, self.p, nv, tab, z_dev.p, C.c_void_p(stream)), "VecMDot (no allocation)")
+
     def dotnorm2(self, t):                  # VecDotNorm2(s, t) -> (s.t, t.t)
         a, b = C.c_double(), C.c_double()
         _chk(lib.b200_vec_dotnorm2(self.n, self.p, t.p, C.byref(a), C.byref(b)), "VecDotNorm2")

@@ -7,6 +7,7 @@
  * (deterministic run to run; differs from the reference BLAS only in summation order).
  */
 #include "b200_internal.h"
+#include <mutex>
 
 #define EW_THREADS 256
 #define RED_THREADS 512
@@ -541,3 +542,88 @@ static int mdot_impl(int n, const double *x, int nv, const double *const *y, dou
 }
 extern "C" int b200_vec_mdot(int n, const double *x, int nv, const double *const *y, double *z) { return mdot_impl(n, x, nv, y, z, true); }
 extern "C" int b200_vec_mdot_local(int n, const double *x, int nv, const double *const *y, double *z) { return mdot_impl(n, x, nv, y, z, false); }
+
+/* ------------------------------------------------------------------------------------------------ VecMDot, no allocation
+ * b200_vec_mdot_noalloc: the mdot_kernel above for callers that may not allocate (CUDA graph capture, serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * It does not need b200_init (which allocates) and calls no cudaMalloc/cudaFree or allocating library routine:
+ *  - the per-CTA partial sums and the last-CTA ticket live in the file-scope device array below, which every GPU
+ *    that loads the library holds until exit: 256 B header + B200_NOALLOC_MAX_CTAS x B200_NOALLOC_MAX_NV doubles
+ *    (148.25 KB);
+ *  - the y pointers travel in the kernel's argument block (MdotArgs), the nv results are written to a DEVICE buffer
+ *    the caller passes, on the stream the caller passes; nothing is read back and nothing synchronises.
+ * Limits: nv <= B200_NOALLOC_MAX_NV (one launch), n <= B200_NOALLOC_MAX_N, reduction grid <= B200_NOALLOC_MAX_CTAS.
+ * Every call on a device shares the array: the ticket word is cleared on the stream before each launch (a call that
+ * died half way would otherwise leave it counting), the partials are fully rewritten by each launch before they are
+ * read.  Two calls that overlap on the GPU (different streams, no ordering between them) race on it. */
+#define B200_NOALLOC_MAX_NV    MDOT_CHUNK
+#define B200_NOALLOC_MAX_CTAS  B200_RED_MAXBLK
+#define B200_NOALLOC_MAX_N     (1 << 30)
+#define B200_NOALLOC_HEADER    32                 /* doubles: 256 B holding the ticket word                                */
+#define B200_NOALLOC_MAXDEV    64
+
+static __device__ __align__(256) double b200_noalloc_scratch[B200_NOALLOC_HEADER + B200_NOALLOC_MAX_CTAS * B200_NOALLOC_MAX_NV];
+
+/* In host code the array's name is only a stand-in for the symbol, not a device address: each device's address is
+ * looked up once, with that device current, and that pointer is what the kernel is given. */
+static double *g_noalloc_addr[B200_NOALLOC_MAXDEV];
+static std::mutex g_noalloc_mutex;
+
+static int noalloc_scratch(double **ptr)
+{
+  int dev = -1;
+  B200_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= B200_NOALLOC_MAXDEV) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "device ordinal %d outside 0..%d", dev, B200_NOALLOC_MAXDEV - 1);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (!g_noalloc_addr[dev]) {
+    double *p = NULL;
+    B200_CUDA(cudaGetSymbolAddress((void **)&p, b200_noalloc_scratch));
+    if (!p) return b200_seterr(B200_ERR_LIB, "cudaGetSymbolAddress gave a null address on device %d", dev);
+    g_noalloc_addr[dev] = p;
+  }
+  *ptr = g_noalloc_addr[dev];
+  return 0;
+}
+
+template <int NV>
+static void mdot_launch_noalloc(int g, int n, const double *x, const MdotArgs &args, bool v2, double *scratch, double *out, cudaStream_t st)
+{
+  double   *partials = scratch + B200_NOALLOC_HEADER;
+  unsigned *ticket   = reinterpret_cast<unsigned *>(scratch);
+  if (v2) mdot_kernel<NV, true><<<g, MDOT_THREADS, 0, st>>>(n, x, args, partials, ticket, out);
+  else    mdot_kernel<NV, false><<<g, MDOT_THREADS, 0, st>>>(n, x, args, partials, ticket, out);
+}
+
+extern "C" int b200_vec_mdot_noalloc(int n, const double *x, int nv, const double *const *y, double *z_dev, void *cuda_stream)
+{
+  if (nv < 0) return b200_seterr(B200_ERR_ARG_OUTOFRANGE, "nv = %d", nv);
+  if (nv > B200_NOALLOC_MAX_NV)
+    return b200_seterr(B200_ERR_ARG_SIZ, "b200_vec_mdot_noalloc: nv = %d exceeds the %d vectors its static scratch holds (use b200_vec_mdot)", nv, B200_NOALLOC_MAX_NV);
+  if (n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative vector length");
+  if (n > B200_NOALLOC_MAX_N)
+    return b200_seterr(B200_ERR_ARG_SIZ, "b200_vec_mdot_noalloc: n = %d exceeds the maximum %d (use b200_vec_mdot)", n, B200_NOALLOC_MAX_N);
+  if (nv == 0) return 0;
+  if (!z_dev || !y || (n > 0 && !x)) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
+  bool v2 = aligned16(x);
+  MdotArgs args;
+  for (int v = 0; v < nv; v++) {
+    if (n > 0 && !y[v]) return b200_seterr(B200_ERR_ARG_NULL, "null device vector y[%d]", v);
+    args.y[v] = y[v];
+    v2 = v2 && aligned16(y[v]);
+  }
+  for (int v = nv; v < MDOT_CHUNK; v++) args.y[v] = NULL;
+  const int g = b200_red_grid(v2 ? (n + 1) / 2 : n, MDOT_THREADS, 2);       /* the grid b200_vec_mdot uses: same sums, same order */
+  if (g > B200_NOALLOC_MAX_CTAS)
+    return b200_seterr(B200_ERR_ARG_SIZ, "b200_vec_mdot_noalloc: %d CTAs exceed the %d its static scratch holds", g, B200_NOALLOC_MAX_CTAS);
+  double *scratch = NULL;
+  B200_CHK(noalloc_scratch(&scratch));
+  cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : (g_b200.inited ? g_b200.stream : (cudaStream_t)0);
+  B200_CUDA(cudaMemsetAsync(scratch, 0, B200_NOALLOC_HEADER * sizeof(double), st));
+  switch (nv) {
+#define MD(N) case N: mdot_launch_noalloc<N>(g, n, x, args, v2, scratch, z_dev, st); break;
+    MD(1) MD(2) MD(3) MD(4) MD(5) MD(6) MD(7) MD(8) MD(9) MD(10) MD(11) MD(12) MD(13) MD(14) MD(15) MD(16)
+#undef MD
+  }
+  B200_LAUNCHED(1);
+  return 0;
+}
