@@ -146,6 +146,7 @@ void b200_mpiaij_fused_dotparts(b200_mat A, const double **p, int *n);
 void b200_mpiaij_fused_free(b200_mat A);
 
 /* internal cross-file entry points */
+void b200_reduce_arm(int nvals);   /* before the launch: stamp nvals result slots so that b200_reduce_finish can poll them (0 = do not poll) */
 int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_max /*0 sum, 1 max*/);
 int b200_comm_allreduce_dev(double *dvals, int n, int op_max);
 int b200_mpiaij_exchange_begin(b200_mat A, const double *x);

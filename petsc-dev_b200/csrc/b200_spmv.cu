@@ -821,6 +821,7 @@ extern "C" int b200_mat_mult_dot(b200_mat A, const double *x, double *y, double 
   B200_NEED_INIT();
   if (!A || !x || !y || !xdoty) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   if (A->kind != 0 || A->A.m != A->A.n || A->A.compressed || A->A.nstrips > 1) return b200_seterr(B200_ERR_SUP, "fused MatMult+dot needs a square sequential matrix stored as one block");
+  b200_reduce_arm(0);          /* not stamped: the product's dot may reach its slot in two steps, so wait for the stream */
   B200_CHK(b200_seq_mult(&A->A, x, NULL, y, false, g_b200.d_res));
   return b200_reduce_finish(1, xdoty, false, 0);
 }

@@ -313,6 +313,9 @@ __device__ __forceinline__ void block_finish(double (&acc)[NV], double *partials
   }
   __syncthreads();
   if (!s_last) return;
+  /* every CTA has taken its ticket: reset it now, by the thread that writes the results below, so that the reset is
+     ordered before them (b200_reduce_finish lets the host go on as soon as it sees the results) */
+  if (threadIdx.x == 0) *ticket = 0;
   __threadfence();
 #pragma unroll
   for (int v = 0; v < NV; v++) {
@@ -328,7 +331,6 @@ __device__ __forceinline__ void block_finish(double (&acc)[NV], double *partials
       if (lane == 0) out[v] = q;
     }
   }
-  if (threadIdx.x == 0) *ticket = 0;
 }
 
 enum { R_DOT, R_SUMSQ, R_ASUM, R_AMAX, R_ASUM_SUMSQ, R_DOTNORM2 };
@@ -383,20 +385,70 @@ __global__ void __launch_bounds__(RED_THREADS) red_kernel(int n, const double *_
 
 /* Bring nvals reduced values (at g_b200.d_res when single rank, g_b200.d_scal when they still need the cross-rank
  * reduction) to the host.  This is the one synchronisation point of VecDot/VecNorm/VecMDot, as in the reference
- * where the result must be valid on return (cg.c:207-220). */
+ * where the result must be valid on return (cg.c:207-220).
+ *
+ * Single rank: the last CTA writes the results straight into mapped pinned memory, so the host does not need the
+ * stream's completion signal, only the values.  b200_reduce_arm() stamps the slots with a NaN payload no reduction
+ * produces BEFORE the launch; b200_reduce_finish() spins on the slots and returns as soon as every one has changed
+ * (the kernel's few remaining instructions — the ticket reset — finish behind it in stream order).  Every 1024 spins
+ * the stream is queried: a kernel that faulted is reported, and a stream that has completed with a slot still
+ * stamped (input that carries the very same payload) falls through to the plain synchronise below, as does
+ * everything with B200_REDUCE_POLL=0. */
+#define B200_RES_STAMP 0x7ff4b200dead5eedULL           /* signalling-NaN pattern: arithmetic results are quiet NaNs */
+static int g_res_armed = 0;
+static int g_res_poll  = -1;
+
+void b200_reduce_arm(int nvals)
+{
+  B200Ctx &c = g_b200;
+  if (g_res_poll < 0) { const char *e = getenv("B200_REDUCE_POLL"); g_res_poll = (e && !atoi(e)) ? 0 : 1; }
+  g_res_armed = 0;
+  if (!g_res_poll || !c.inited || nvals < 1 || nvals > B200_RES_SLOTS) return;
+  volatile unsigned long long *h = reinterpret_cast<volatile unsigned long long *>(c.h_res);
+  for (int v = 0; v < nvals; v++) h[v] = B200_RES_STAMP;
+  g_res_armed = nvals;
+}
+
 int b200_reduce_finish(int nvals, double *result_host, bool allreduce, int op_max)
 {
   B200Ctx &c = g_b200;
+  const int armed = g_res_armed;
+  g_res_armed = 0;
   if (allreduce && c.size > 1) {
     B200_CHK(b200_comm_allreduce_dev(c.d_scal, nvals, op_max));
     B200_CUDA(cudaMemcpyAsync(c.h_res, c.d_scal, sizeof(double) * nvals, cudaMemcpyDeviceToHost, c.stream));
+  } else if (armed >= nvals && nvals > 0) {
+    volatile unsigned long long *h = reinterpret_cast<volatile unsigned long long *>(c.h_res);
+    unsigned spins = 0;
+    int v = nvals - 1;                                   /* the highest slot is written last */
+    while (v >= 0) {
+      if (h[v] != B200_RES_STAMP) { v--; continue; }
+      if ((++spins & 1023u) == 0) {
+        cudaError_t q = cudaStreamQuery(c.stream);
+        if (q == cudaSuccess) break;
+        if (q != cudaErrorNotReady) return b200_cuda_err(q, "reduction kernel", __FILE__, __LINE__);
+      }
+#if defined(__x86_64__)
+      __builtin_ia32_pause();
+#endif
+    }
+    if (v < 0) {
+      for (int k = 0; k < nvals; k++) result_host[k] = c.h_res[k];
+      return 0;
+    }
   }
   B200_CUDA(cudaStreamSynchronize(c.stream));
   for (int v = 0; v < nvals; v++) result_host[v] = c.h_res[v];
   return 0;
 }
 
-static inline double *red_out(bool allreduce) { return (allreduce && g_b200.size > 1) ? g_b200.d_scal : g_b200.d_res; }
+/* where a reduction launch writes; call it BEFORE the launch: it stamps the nvals host-visible slots (see above) */
+static inline double *red_out(bool allreduce, int nvals)
+{
+  if (allreduce && g_b200.size > 1) return g_b200.d_scal;
+  b200_reduce_arm(nvals);
+  return g_b200.d_res;
+}
 
 template <int K>
 static int red_launch(int n, const double *x, const double *y, double *out)
@@ -417,7 +469,7 @@ static int dot_impl(int n, const double *x, const double *y, double *r, bool all
   if (!r) return b200_seterr(B200_ERR_ARG_NULL, "null result pointer");
   if (n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative vector length");
   if (n > 0 && (!x || !y)) return b200_seterr(B200_ERR_ARG_NULL, "null device vector");
-  B200_CHK(red_launch<R_DOT>(n, x, y, red_out(allreduce)));
+  B200_CHK(red_launch<R_DOT>(n, x, y, red_out(allreduce, 1)));
   return b200_reduce_finish(1, r, allreduce, 0);
 }
 extern "C" int b200_vec_dot(int n, const double *x, const double *y, double *r) { return dot_impl(n, x, y, r, true); }
@@ -429,7 +481,7 @@ static int norm_impl(int n, const double *x, int type, double *r, bool allreduce
   if (!r) return b200_seterr(B200_ERR_ARG_NULL, "null result pointer");
   if (n < 0) return b200_seterr(B200_ERR_ARG_SIZ, "negative vector length");
   if (n > 0 && !x) return b200_seterr(B200_ERR_ARG_NULL, "null device vector");
-  double *out = red_out(allreduce);
+  double *out = red_out(allreduce, 2);
   switch (type) {
   case B200_NORM_2:
   case B200_NORM_FROBENIUS:                       /* sqrt(ddot(x,x)): bvec2.c:617-618; MPI: sum of squares, then sqrt pvec2.c:59-62 */
@@ -459,7 +511,7 @@ extern "C" int b200_vec_dotnorm2(int n, const double *s, const double *t, double
   B200_NEED_INIT();
   if (!dp || !nm) return b200_seterr(B200_ERR_ARG_NULL, "null result pointer");
   double r[2];
-  B200_CHK(red_launch<R_DOTNORM2>(n, s, t, red_out(true)));
+  B200_CHK(red_launch<R_DOTNORM2>(n, s, t, red_out(true, 2)));
   B200_CHK(b200_reduce_finish(2, r, true, 0));
   *dp = r[0]; *nm = r[1];
   return 0;
@@ -525,7 +577,7 @@ static int mdot_impl(int n, const double *x, int nv, const double *const *y, dou
   if (!z || !y || (n > 0 && !x)) return b200_seterr(B200_ERR_ARG_NULL, "null argument");
   bool v2 = aligned16(x);
   for (int v = 0; v < nv; v++) v2 = v2 && aligned16(y[v]);
-  double *out = red_out(allreduce);
+  double *out = red_out(allreduce, nv);
   for (int done = 0; done < nv;) {
     const int take = (nv - done < MDOT_CHUNK) ? nv - done : MDOT_CHUNK;
     MdotArgs args;

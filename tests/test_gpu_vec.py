@@ -139,3 +139,19 @@ def test_large_vector_properties(gpu, P):
     assert abs(x.norm() - 0.5 * np.sqrt(n)) <= 1e-12 * np.sqrt(n)
     y.axpy(4.0, x)                                      # -2 + 4*0.5 = 0
     assert y.norm(gpu.NORM_INFINITY) == 0.0
+
+
+def test_reductions_return_when_the_input_carries_the_poll_stamp(gpu):
+    """b200_reduce_finish polls the mapped result slots for a change from a signalling-NaN stamp (b200_vec.cu): input that
+    holds the very same bit pattern must still come back (as NaN), and the slots must be usable afterwards."""
+    n = 4099
+    h = np.full(n, 0.25)
+    h.view(np.uint64)[17] = 0x7FF4B200DEAD5EED
+    x, y = gpu.Vec(n, h), gpu.Vec(n)
+    y.set(1.0)
+    for t in (gpu.NORM_1, gpu.NORM_2, gpu.NORM_INFINITY):
+        assert np.isnan(x.norm(t))                          # bvec2.c:626: a NaN entry makes every norm NaN
+    assert all(np.isnan(v) for v in x.norm(gpu.NORM_1_AND_2))
+    assert np.isnan(x.dot(y)) and np.isnan(x.mdot([y, x, y])).all()
+    assert y.norm(gpu.NORM_1) == float(n) and y.dot(y) == float(n)
+    assert np.array_equal(y.mdot([y] * 20), np.full(20, float(n)))      # two launches, 20 slots
