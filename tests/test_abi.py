@@ -57,3 +57,23 @@ def test_no_cpu_fallback(pb):
     ip = np.array([0, 1], np.int32); j = np.array([0], np.int32); a = np.array([1.0])
     with pytest.raises(pb.PetscB200Error):
         pb.Mat.from_csr(1, 1, ip, j, a)
+
+
+def test_noalloc_mdot_checks_its_limits_before_touching_a_device(pb):
+    """b200_vec_mdot_noalloc validates sizes and pointers first: beyond the static scratch (16 vectors, 2^30 entries) it
+    answers PETSC_ERR_ARG_SIZ with a message that names the limit; without a device the valid call fails loudly."""
+    f = pb.lib.b200_vec_mdot_noalloc
+    dummy = (pb.c_dp * 17)()
+    x = C.cast(C.c_void_p(256), pb.c_dp)          # never dereferenced by the argument checks
+    assert f(8, x, 17, dummy, x, C.c_void_p(None)) == 60 and b"exceeds the 16 vectors" in pb.lib.b200_last_error()
+    assert f((1 << 30) + 1, x, 1, dummy, x, C.c_void_p(None)) == 60 and b"exceeds the maximum" in pb.lib.b200_last_error()
+    assert f(-1, x, 1, dummy, x, C.c_void_p(None)) == 60
+    assert f(8, x, -1, dummy, x, C.c_void_p(None)) == 63
+    assert f(8, x, 0, None, None, C.c_void_p(None)) == 0
+    assert f(8, x, 1, dummy, None, C.c_void_p(None)) == 85
+    assert f(8, x, 1, dummy, x, C.c_void_p(None)) == 85          # y[0] is a null pointer
+    n = C.c_int()
+    if pb.lib.b200_device_count(C.byref(n)) == 0 and n.value > 0:
+        return
+    dummy[0] = x
+    assert f(8, x, 1, dummy, x, C.c_void_p(None)) == 76          # no device: PETSC_ERR_LIB, nothing computed
